@@ -1,0 +1,68 @@
+// Exhaustive / sampled comparison of csrc/exact_math.h (C build) against the host libm.
+// Build: gcc -O2 -mfma -ffp-contract=off -fopenmp -I<pkg>/csrc scripts/check_exact_math.c -lm -o /tmp/check_exact_math
+//        (-mfma only so the one deliberate fma in the range reduction is an instruction, not a libm call;
+//         -ffp-contract=off keeps gcc from fusing anything else)
+// Usage: check_exact_math [full]   (default: strided subset that finishes in a few seconds)
+// Result in the build container (glibc 2.39): `full` = all 4,278,190,080 finite floats for sinf/cosf and
+// 4e9 random pairs for atan2f/hypotf, 0 mismatches, ~80 s on 8 threads.
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "exact_math.h"
+
+static uint64_t splitmix(uint64_t* s)
+{
+    uint64_t z = (*s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+int main(int argc, char** argv)
+{
+    const int full = argc > 1 && !strcmp(argv[1], "full");
+    const uint64_t stride = full ? 1 : 257;
+    uint64_t bad_sin = 0, bad_cos = 0, bad_sc = 0, n = 0;
+#pragma omp parallel for reduction(+ : bad_sin, bad_cos, bad_sc, n) schedule(static)
+    for (uint64_t b = 0; b < 0x100000000ull; b += stride) {
+        const uint32_t bits = (uint32_t)b;
+        if ((bits & 0x7f800000u) == 0x7f800000u) continue; // inf / nan
+        const float x = xm_u2f(bits);
+        const float s0 = sinf(x), c0 = cosf(x);
+        const float s1 = xm_sinf(x), c1 = xm_cosf(x);
+        float s2, c2;
+        xm_sincosf(x, &s2, &c2);
+        bad_sin += xm_f2u(s0) != xm_f2u(s1);
+        bad_cos += xm_f2u(c0) != xm_f2u(c1);
+        bad_sc += (xm_f2u(s2) != xm_f2u(s1)) || (xm_f2u(c2) != xm_f2u(c1));
+        ++n;
+    }
+    printf("sinf: %llu mismatches, cosf: %llu mismatches, sincos-internal: %llu of %llu finite floats\n",
+           (unsigned long long)bad_sin, (unsigned long long)bad_cos, (unsigned long long)bad_sc,
+           (unsigned long long)n);
+
+    const uint64_t pairs = full ? 4000000000ull : 40000000ull;
+    uint64_t bad_at = 0, bad_hy = 0;
+#pragma omp parallel for reduction(+ : bad_at, bad_hy) schedule(static)
+    for (uint64_t chunk = 0; chunk < 4000; ++chunk) {
+        uint64_t st = 0x1234 + chunk * 0x51ED27ull;
+        for (uint64_t i = 0; i < pairs / 4000; ++i) {
+            const uint64_t r = splitmix(&st);
+            uint32_t a = (uint32_t)r, b = (uint32_t)(r >> 32);
+            // keep exponents in a window that FFT bins can produce, plus some wild ones
+            if (i & 7) {
+                a = (a & 0x807fffffu) | ((100u + ((a >> 23) & 63u)) << 23);
+                b = (b & 0x807fffffu) | ((100u + ((b >> 23) & 63u)) << 23);
+            }
+            const float y = xm_u2f(a), x = xm_u2f(b);
+            if (y != y || x != x) continue;
+            bad_at += xm_f2u(atan2f(y, x)) != xm_f2u(xm_atan2f(y, x));
+            bad_hy += xm_f2u(hypotf(y, x)) != xm_f2u(xm_hypotf(y, x));
+        }
+    }
+    printf("atan2f: %llu mismatches, hypotf: %llu mismatches of %llu pairs\n",
+           (unsigned long long)bad_at, (unsigned long long)bad_hy, (unsigned long long)pairs);
+    return (bad_sin || bad_cos || bad_sc || bad_at || bad_hy) ? 1 : 0;
+}
