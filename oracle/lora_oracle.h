@@ -119,11 +119,26 @@ typedef struct {
 /* LoRa-SDR/LoRaEncoder.cpp:132-233.  Returns symbol count (or the needed count when symbols==NULL). */
 size_t orc_chain_encode(const orc_chain_cfg* c, const uint8_t* payload, size_t len,
                         uint16_t* symbols, size_t cap);
-/* LoRa-SDR/LoRaDecoder.cpp:196-397.  Returns bytes emitted, or -1 when the block drops the packet,
- * or -2 when it returns without output (fewer than 8 symbols).  With interleaving off the Gray'd
- * symbols are written to out as little-endian uint16 and 2*numSymbols is returned. */
+/* What the decoder saw on the way; filled as far as the block got before returning. */
+typedef struct {
+    int drop_line;     /* 0 = emitted; else the LoRaDecoder.cpp line of the `return this->drop()` taken */
+    int parity_error;  /* `error` flag: some codeword had a non-zero syndrome / parity failure        */
+    int uncorrectable; /* `bad` flag: some Hamming(8,4) word had a 2-bit syndrome                     */
+    int hdr_length;    /* explicit mode: bytes[0]                                                      */
+    int hdr_has_crc;   /* explicit mode: bytes[1] & 1                                                  */
+    int hdr_rdd;       /* explicit mode: (bytes[1] >> 1) & 7                                           */
+    int hdr_checksum;  /* explicit mode: bytes[2] after XOR with headerChecksum (0 = header valid)      */
+    int crc_present;   /* a CRC was computed                                                           */
+    int crc_ok;        /* computed CRC == packet CRC                                                   */
+} orc_chain_info;
+
+/* LoRa-SDR/LoRaDecoder.cpp:196-397.  Returns bytes emitted; -1 when the block drops the packet
+ * (info->drop_line says where); -2 when it returns without output (fewer than 8 symbols, :208);
+ * -3 where the reference itself is undefined (explicit header, no CRC bit, hdr off and length < 2:
+ * `dataLength -= 5` wraps, :381-384).  With interleaving off the Gray'd symbols are written to out as
+ * little-endian uint16 and 2*numSymbols is returned (:264-270). */
 long   orc_chain_decode(const orc_chain_cfg* c, const uint16_t* symbols, size_t nsym,
-                        uint8_t* out, size_t cap);
+                        uint8_t* out, size_t cap, orc_chain_info* info);
 
 #ifdef __cplusplus
 }
