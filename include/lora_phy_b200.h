@@ -1,0 +1,181 @@
+/* lora_phy_b200.h -- C ABI of the B200 LoRa receive path (liblora_phy_b200.so).
+ *
+ * This is the drop-in boundary.  Plain pointers and sizes, no C++ or torch types.  The reference has no
+ * FFI of its own (it is a C++ static library, CMakeLists.txt:12-21); each entry point below names the
+ * reference function it replaces, and include/lora_phy/phy.hpp wraps them back into the reference's C++
+ * names so runners/rx_runner.cpp and tx_runner.cpp build unchanged.
+ *
+ * Conventions
+ *   - Every function returns LORA_B200_OK (0) or a negative code; lora_b200_last_error() gives text.
+ *   - `d_` pointers are device pointers on the context's GPU, `h_` pointers are host pointers.
+ *   - Device entry points are stream-ordered on `stream` (a cudaStream_t passed as void*; NULL = the
+ *     legacy default stream) and never synchronise or allocate after the first call at a given size.
+ *   - IQ is interleaved little-endian float32 (re, im) = std::complex<float>; symbols are uint16_t.
+ *   - There is no CPU fallback anywhere: with no usable CUDA device every call fails with
+ *     LORA_B200_ECUDA.
+ */
+#ifndef LORA_PHY_B200_H
+#define LORA_PHY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LORA_B200_OK 0
+#define LORA_B200_EINVAL (-1) /* bad argument (the reference returns -1 for these too, phy.cpp:181-190) */
+#define LORA_B200_ECUDA (-2)  /* CUDA runtime error or no device */
+#define LORA_B200_ENOMEM (-3)
+
+typedef struct lora_b200_ctx lora_b200_ctx;
+typedef struct { float re, im; } lora_b200_c32;
+
+/* Which reference entry point's semantics demod follows. */
+enum {
+    /* lora_phy::demodulate, src/phy/phy.cpp:178-239: offsets estimated on the RAW first two symbols,
+     * every window multiplied by the down-chirp table, then by the CFO rotation. */
+    LORA_B200_DEMOD_WORKSPACE = 0,
+    /* lora_phy::lora_demodulate, src/phy/LoRaDemod.cpp:49-195: input already dechirped by the caller;
+     * max-abs normalisation when any |re| or |im| exceeds 1, offsets estimated on the normalised data. */
+    LORA_B200_DEMOD_LEGACY = 1,
+    /* The pipeline of tests/performance_test.cpp:103-116 and tests/e2e_chain_test.cpp:79-104: caller-side
+     * dechirp by the genChirp down table, then lora_demodulate -- with the dechirped copy never written
+     * to memory.  Bit-identical to running those two steps on the CPU. */
+    LORA_B200_DEMOD_LEGACY_DECHIRP = 2
+};
+
+typedef struct {
+    unsigned sf;     /* 1..12 (N = 1 << sf <= 4096, include/lora_phy/kissfft.hh:34) */
+    unsigned bw_hz;  /* 125000, 250000 or 500000 (phy.hpp:36-40)                      */
+    unsigned osr;    /* oversampling ratio, 0 means 1                                 */
+    int window;      /* 0 = none, 1 = Hann (phy.hpp:29-32)                            */
+    int device;      /* CUDA device ordinal, -1 = current device                      */
+} lora_b200_config;
+
+/* Per-packet result of demod, 16 bytes. */
+typedef struct {
+    float cfo;           /* lora_metrics::cfo (phy.hpp:65-69)                                          */
+    float time_offset;   /* lora_metrics::time_offset                                                  */
+    float max_amp;       /* legacy modes: max(|re|,|im|) over the packet (LoRaDemod.cpp:61-67), else 0 */
+    uint8_t sync_word;   /* high nibbles of the first two windows (phy.cpp:235-237)                    */
+    uint8_t normalised;  /* legacy modes: 1 when max_amp > 1 and samples were scaled                   */
+    uint16_t n_symbols;  /* symbols written for this packet                                            */
+} lora_b200_pkt_metrics;
+
+/* Configuration of the full coding chain; mirrors the setters of the Pothos blocks
+ * (LoRa-SDR/LoRaDecoder.cpp:131-189, LoRa-SDR/LoRaEncoder.cpp:99-130). */
+typedef struct {
+    unsigned sf;
+    unsigned ppm;          /* 0 = full symbol set; sf-2 for low-data-rate optimisation */
+    unsigned rdd;          /* 0..4 = coding rate 4/4 .. 4/8                             */
+    int explicit_header;
+    int crc;               /* encoder: append CRC; decoder: drop on CRC mismatch (crcc) */
+    int whitening;         /* encoder only                                              */
+    int interleaving;      /* decoder only                                              */
+    int error_check;       /* decoder only                                              */
+    int hdr_out;           /* decoder only                                              */
+    unsigned data_length;  /* decoder, implicit header mode                             */
+} lora_b200_chain_cfg;
+
+/* Per-packet result of the chain decoder, 16 bytes. */
+typedef struct {
+    int16_t n_bytes;       /* bytes emitted; -1 dropped, -2 no output (< 8 symbols), -3 reference-undefined */
+    int16_t drop_line;     /* 0, or the LoRaDecoder.cpp line of the drop() taken                            */
+    uint8_t parity_error;  /* `error` flag   */
+    uint8_t uncorrectable; /* `bad` flag     */
+    uint8_t hdr_length, hdr_has_crc, hdr_rdd, hdr_checksum;
+    uint8_t crc_present, crc_ok;
+    uint8_t reserved[4];
+} lora_b200_chain_result;
+
+#define LORA_B200_PAYLOAD_STRIDE 264 /* bytes reserved per packet by the chain decoder (<= 255+3+2, padded) */
+
+/* ---- lifetime ------------------------------------------------------------------------------------------ */
+/* Replaces lora_phy::init (phy.cpp:26-49) / lora_demod_init (LoRaDemod.cpp:10-32): builds the twiddle,
+ * down-chirp and window tables on the host exactly as the reference does and uploads them. */
+int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx** out);
+void lora_b200_ctx_destroy(lora_b200_ctx* ctx);
+const char* lora_b200_last_error(void);
+/* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
+unsigned long long lora_b200_launch_count(void);
+/* Copies of the host-built tables, for tests: table 0 twiddles, 1 down-chirp (n complex), 2 window (n floats). */
+int lora_b200_ctx_table(const lora_b200_ctx* ctx, int table, void* h_out, size_t n);
+
+/* ---- receive path, device buffers ------------------------------------------------------------------------- */
+/* demodulate / lora_demodulate over a batch of equal-length packets.
+ *   d_iq              n_packets packets, packet p starting at d_iq + p*packet_stride
+ *   samples_per_packet the `sample_count` each reference call would see
+ *   d_symbols         packet p's symbols at d_symbols + p*symbol_stride: total-2 of them (the two sync
+ *                     windows are stripped, phy.cpp:226-233), or all when total < 2 in legacy mode
+ *   d_peaks           optional, n_packets * total floats: max |X[k]|^2 of every window incl. sync
+ *   d_metrics         optional, one record per packet
+ * WORKSPACE mode requires samples_per_packet % (N*osr) == 0 and >= 2 symbols, as phy.cpp:186-190 does. */
+int lora_b200_demod_batch(lora_b200_ctx* ctx, int mode, const lora_b200_c32* d_iq, size_t n_packets,
+                          size_t samples_per_packet, size_t packet_stride, uint16_t* d_symbols,
+                          size_t symbol_stride, float* d_peaks, lora_b200_pkt_metrics* d_metrics,
+                          void* stream);
+
+/* lora_phy::estimate_offsets (phy.cpp:78-145) over a batch; writes cfo/time_offset of d_metrics. */
+int lora_b200_estimate_batch(lora_b200_ctx* ctx, const lora_b200_c32* d_iq, size_t n_packets,
+                             size_t samples_per_packet, size_t packet_stride,
+                             lora_b200_pkt_metrics* d_metrics, void* stream);
+
+/* lora_phy::decode / lora_decode (phy.cpp:241-256, src/phy/LoRaDecoder.cpp:6-19): Hamming(8,4) pairs to
+ * bytes plus the CRC flag.  Packet p: symbols at d_symbols + p*symbol_stride, bytes at d_bytes + p*byte_stride. */
+int lora_b200_decode_batch(lora_b200_ctx* ctx, const uint16_t* d_symbols, size_t n_packets,
+                           size_t symbols_per_packet, size_t symbol_stride, uint8_t* d_bytes,
+                           size_t byte_stride, uint8_t* d_crc_ok, void* stream);
+
+/* LoRaDecoder::work (LoRa-SDR/LoRaDecoder.cpp:196-397): Gray, diagonal deinterleave, dewhiten, Hamming /
+ * parity, header, CRC.  Payload of packet p at d_payload + p*LORA_B200_PAYLOAD_STRIDE. */
+int lora_b200_chain_decode_batch(lora_b200_ctx* ctx, const lora_b200_chain_cfg* cfg,
+                                 const uint16_t* d_symbols, size_t n_packets, size_t symbols_per_packet,
+                                 size_t symbol_stride, uint8_t* d_payload,
+                                 lora_b200_chain_result* d_results, void* stream);
+
+/* ---- transmit side (used to synthesise inputs, and by tx_runner) ------------------------------------------- */
+/* lora_encode (src/phy/LoRaEncoder.cpp:6-18). */
+int lora_b200_encode_batch(lora_b200_ctx* ctx, const uint8_t* d_bytes, size_t n_packets,
+                           size_t bytes_per_packet, size_t byte_stride, uint16_t* d_symbols,
+                           size_t symbol_stride, void* stream);
+/* LoRaEncoder::work (LoRa-SDR/LoRaEncoder.cpp:161-233); every packet has payload_len bytes.
+ * Returns the symbol count per packet through *symbols_per_packet (may be queried with d_symbols NULL). */
+int lora_b200_chain_encode_batch(lora_b200_ctx* ctx, const lora_b200_chain_cfg* cfg,
+                                 const uint8_t* d_payload, size_t n_packets, size_t payload_len,
+                                 size_t payload_stride, uint16_t* d_symbols, size_t symbol_stride,
+                                 size_t* symbols_per_packet, void* stream);
+/* lora_modulate (src/phy/LoRaMod.cpp:8-43): [sync0][sync1][symbols...] chirps with the reference's float32
+ * phase-accumulator recurrence.  Packet p's (symbols_per_packet+2)*N*osr samples at d_iq + p*packet_stride. */
+int lora_b200_modulate_batch(lora_b200_ctx* ctx, const uint16_t* d_symbols, size_t n_packets,
+                             size_t symbols_per_packet, size_t symbol_stride, float amplitude,
+                             uint8_t sync, lora_b200_c32* d_iq, size_t packet_stride, void* stream);
+/* Adds complex white Gaussian noise in place: per-component sigma/sqrt(2) with sigma = 10^(-snr_db/20)
+ * (tests/awgn_sweep_gtest.cpp:76-80).  d_snr_db holds one SNR per packet.  Counter-based generator, so the
+ * result depends only on (seed, packet, sample). */
+int lora_b200_awgn_batch(lora_b200_ctx* ctx, lora_b200_c32* d_iq, size_t n_packets,
+                         size_t samples_per_packet, size_t packet_stride, const float* d_snr_db,
+                         uint64_t seed, void* stream);
+
+/* ---- host-buffer entry points (what include/lora_phy/phy.hpp calls) ------------------------------------------ */
+/* One packet, host pointers; copies in, runs the kernels above, copies out, synchronises. */
+int lora_b200_demodulate_host(lora_b200_ctx* ctx, int mode, const lora_b200_c32* h_iq, size_t sample_count,
+                              uint16_t* h_symbols, size_t symbol_cap, size_t* n_symbols,
+                              lora_b200_pkt_metrics* h_metrics);
+int lora_b200_estimate_host(lora_b200_ctx* ctx, const lora_b200_c32* h_iq, size_t sample_count,
+                            float* cfo, float* time_offset);
+int lora_b200_modulate_host(lora_b200_ctx* ctx, const uint16_t* h_symbols, size_t symbol_count,
+                            float amplitude, uint8_t sync, lora_b200_c32* h_iq, size_t iq_cap,
+                            size_t* n_samples);
+/* Batched host-buffer demod + chain decode: the end-to-end call bench.py times (pinned or pageable host
+ * memory in, payloads and results out). */
+int lora_b200_receive_host(lora_b200_ctx* ctx, int mode, const lora_b200_chain_cfg* cfg,
+                           const lora_b200_c32* h_iq, size_t n_packets, size_t samples_per_packet,
+                           uint8_t* h_payload, lora_b200_chain_result* h_results,
+                           lora_b200_pkt_metrics* h_metrics);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,527 @@
+// capi.cu -- the extern "C" boundary declared in include/lora_phy_b200.h.
+//
+// Thin by design: argument checks that mirror the reference's guards, table upload at context creation,
+// grow-only device scratch (nothing is allocated once a batch size has been seen, the GPU counterpart of
+// the reference's zero-allocation rule, tests/no_alloc_test.cpp), and kernel launches.  No arithmetic of
+// the receive path happens on the host, and there is no CPU fallback: a missing device is an error.
+#include "lora_phy_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "code_kernels.h"
+#include "demod_kernels.h"
+#include "host_tables.h"
+#include "mod_kernels.h"
+
+using namespace lora_b200;
+
+static thread_local std::string g_error;
+
+static int fail(int code, const char* what, cudaError_t e = cudaSuccess)
+{
+    g_error = what;
+    if (e != cudaSuccess) { g_error += ": "; g_error += cudaGetErrorString(e); }
+    return code;
+}
+
+#define CU(call)                                                          \
+    do {                                                                  \
+        cudaError_t e_ = (call);                                          \
+        if (e_ != cudaSuccess) return fail(LORA_B200_ECUDA, #call, e_);   \
+    } while (0)
+
+// A grow-only device (or pinned host) buffer.
+struct Buf {
+    void* p = nullptr;
+    size_t cap = 0;
+    bool pinned = false;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { pinned ? cudaFreeHost(p) : cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 4; // head-room so slowly growing batches do not reallocate each time
+        cudaError_t e = pinned ? cudaMallocHost(&p, want) : cudaMalloc(&p, want);
+        if (e != cudaSuccess) { want = bytes; e = pinned ? cudaMallocHost(&p, want) : cudaMalloc(&p, want); }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p) { pinned ? cudaFreeHost(p) : cudaFree(p); }
+        p = nullptr; cap = 0;
+    }
+    template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct lora_b200_ctx {
+    lora_b200_config cfg{};
+    int device = 0, sm_count = 148;
+    int n = 0;
+    float bw_scale = 1.0f, power_scale = 0.0f;
+    std::vector<std::complex<float>> h_tw, h_down;
+    std::vector<float> h_window;
+    float2* d_tw = nullptr;
+    float2* d_down = nullptr;
+    float* d_window = nullptr;   // Hann table, or nullptr when window == none
+    uint8_t* d_whiten = nullptr; // 2 x WHITEN_LEN bytes
+    Buf est, sync_raw;           // per-packet scratch of the demod kernels
+    Buf s_iq, s_sym, s_metrics, s_payload, s_results, s_misc; // staging for the host-buffer entry points
+    Buf h_pin;                   // pinned bounce buffer
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+};
+
+extern "C" const char* lora_b200_last_error(void) { return g_error.c_str(); }
+extern "C" unsigned long long lora_b200_launch_count(void) { return g_launches; }
+
+extern "C" int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx** out)
+{
+    if (!cfg || !out) return fail(LORA_B200_EINVAL, "null argument");
+    if (cfg->sf < 2 || cfg->sf > 12) return fail(LORA_B200_EINVAL, "sf must be 2..12 (N <= 4096, kissfft.hh:34)");
+    if (cfg->bw_hz != 125000 && cfg->bw_hz != 250000 && cfg->bw_hz != 500000)
+        return fail(LORA_B200_EINVAL, "bw_hz must be 125000, 250000 or 500000");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(LORA_B200_ECUDA, "no CUDA device: this library has no CPU path", e);
+    int dev = cfg->device;
+    if (dev < 0) CU(cudaGetDevice(&dev));
+    if (dev >= count) return fail(LORA_B200_EINVAL, "device ordinal out of range");
+    CU(cudaSetDevice(dev));
+
+    lora_b200_ctx* c = new lora_b200_ctx();
+    c->cfg = *cfg;
+    if (c->cfg.osr == 0) c->cfg.osr = 1;
+    c->device = dev;
+    c->n = 1 << cfg->sf;
+    c->bw_scale = static_cast<float>(cfg->bw_hz) / 125000.0f; // phy.hpp:43-49
+    c->power_scale = detector_power_scale(c->n);
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, dev);
+    c->h_tw = build_twiddles(c->n);
+    c->h_down = build_downchirp(c->n, c->bw_scale);
+    c->h_window = build_hann(c->n);
+    c->h_pin.pinned = true;
+    std::vector<uint8_t> wh(2 * WHITEN_LEN);
+    build_whitening(wh.data(), wh.data() + WHITEN_LEN, WHITEN_LEN);
+
+    const size_t nb = sizeof(float2) * c->n;
+    bool ok = cudaMalloc(&c->d_tw, nb) == cudaSuccess && cudaMalloc(&c->d_down, nb) == cudaSuccess &&
+              cudaMalloc(&c->d_whiten, wh.size()) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    if (ok && cfg->window == 1) ok = cudaMalloc(&c->d_window, sizeof(float) * c->n) == cudaSuccess;
+    ok = ok && cudaMemcpy(c->d_tw, c->h_tw.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(c->d_down, c->h_down.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(c->d_whiten, wh.data(), wh.size(), cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok && c->d_window)
+        ok = cudaMemcpy(c->d_window, c->h_window.data(), sizeof(float) * c->n, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (!ok) {
+        const cudaError_t last = cudaGetLastError();
+        lora_b200_ctx_destroy(c);
+        return fail(LORA_B200_ECUDA, "context setup", last);
+    }
+    *out = c;
+    return LORA_B200_OK;
+}
+
+extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_tw); cudaFree(c->d_down); cudaFree(c->d_window); cudaFree(c->d_whiten);
+    for (Buf* b : {&c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
+                   &c->s_misc, &c->h_pin})
+        b->release();
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" int lora_b200_ctx_table(const lora_b200_ctx* c, int table, void* h_out, size_t n)
+{
+    if (!c || !h_out || n != static_cast<size_t>(c->n)) return fail(LORA_B200_EINVAL, "bad table request");
+    switch (table) {
+    case 0: std::memcpy(h_out, c->h_tw.data(), sizeof(float2) * n); return LORA_B200_OK;
+    case 1: std::memcpy(h_out, c->h_down.data(), sizeof(float2) * n); return LORA_B200_OK;
+    case 2: std::memcpy(h_out, c->h_window.data(), sizeof(float) * n); return LORA_B200_OK;
+    default: return fail(LORA_B200_EINVAL, "unknown table");
+    }
+}
+
+// ---- receive path -------------------------------------------------------------------------------------------
+static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, size_t n_packets, size_t count,
+                              size_t packet_stride, uint16_t* d_symbols, size_t symbol_stride, float* d_peaks,
+                              lora_b200_pkt_metrics* d_metrics, cudaStream_t st)
+{
+    const size_t N = static_cast<size_t>(c->n), osr = c->cfg.osr, step = N * osr;
+    const bool legacy = mode != LORA_B200_DEMOD_WORKSPACE;
+    if (mode < 0 || mode > 2) return fail(LORA_B200_EINVAL, "unknown demod mode");
+    if (!d_iq || !d_symbols) return fail(LORA_B200_EINVAL, "null buffer");              // phy.cpp:181
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu) return fail(LORA_B200_EINVAL, "too many packets");
+    if (packet_stride < count) return fail(LORA_B200_EINVAL, "packet_stride < samples_per_packet");
+    const size_t total = count / step;
+    if (!legacy) {
+        if (count % step != 0) return fail(LORA_B200_EINVAL, "sample count not a multiple of N*osr"); // :186
+        if (total < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");                        // :188
+    }
+    if (mode == LORA_B200_DEMOD_LEGACY_DECHIRP && (osr != 1 || count % N != 0))
+        return fail(LORA_B200_EINVAL, "fused caller-dechirp needs osr == 1 and whole symbols");
+    const bool have_sync = total >= 2;
+    const size_t n_out = have_sync ? total - 2 : total;
+    if (symbol_stride < n_out) return fail(LORA_B200_EINVAL, "symbol_stride too small");
+    if (total > 0xffff) return fail(LORA_B200_EINVAL, "more than 65535 symbols per packet");
+
+    CU(c->est.reserve(sizeof(float4) * n_packets));
+    CU(c->sync_raw.reserve(sizeof(uint16_t) * 2 * n_packets));
+    float4* est = c->est.as<float4>();
+    const int np = static_cast<int>(n_packets);
+    CU(launch_fill_est(est, np, st));
+    const bool dechirp_in = mode == LORA_B200_DEMOD_LEGACY_DECHIRP;
+    if (legacy && count > 0) {
+        MaxAbsArgs m{d_iq, packet_stride, count, dechirp_in ? c->d_down : nullptr, c->n, est};
+        CU(launch_maxabs(m, np, st));
+    }
+    if (total > 0) {
+        EstimateArgs ea{};
+        ea.iq = d_iq; ea.packet_stride = packet_stride;
+        ea.symbols = static_cast<int>(total < 2 ? total : 2);
+        ea.osr = static_cast<int>(osr);
+        ea.dechirp = dechirp_in;   // demodulate() estimates on RAW samples (phy.cpp:192-193)
+        ea.use_scale = legacy;
+        ea.legacy_tie = legacy;
+        ea.tw = c->d_tw; ea.down = c->d_down; ea.window = c->d_window;
+        ea.power_scale = c->power_scale;
+        ea.est = est;
+        CU(launch_estimate(static_cast<int>(c->cfg.sf), ea, np, st));
+
+        DemodArgs da{};
+        da.iq = d_iq; da.packet_stride = packet_stride; da.count = count;
+        da.n_windows = static_cast<long long>(n_packets) * static_cast<long long>(total);
+        da.total = static_cast<int>(total);
+        da.osr = static_cast<int>(osr);
+        da.dechirp = mode != LORA_B200_DEMOD_LEGACY;
+        da.use_scale = legacy;
+        da.have_sync = have_sync;
+        da.tw = c->d_tw; da.down = c->d_down; da.window = c->d_window;
+        da.est = est;
+        da.symbols = d_symbols; da.symbol_stride = symbol_stride;
+        da.sync_raw = c->sync_raw.as<uint16_t>();
+        da.peaks = d_peaks;
+        CU(launch_demod(static_cast<int>(c->cfg.sf), da, c->sm_count, st));
+    }
+    if (d_metrics) {
+        FinalizeArgs fa{est, c->sync_raw.as<uint16_t>(), d_metrics, np, static_cast<int>(c->cfg.sf),
+                        have_sync, legacy, static_cast<int>(n_out)};
+        CU(launch_finalize(fa, st));
+    }
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_demod_batch(lora_b200_ctx* c, int mode, const lora_b200_c32* d_iq, size_t n_packets,
+                                     size_t samples_per_packet, size_t packet_stride, uint16_t* d_symbols,
+                                     size_t symbol_stride, float* d_peaks, lora_b200_pkt_metrics* d_metrics,
+                                     void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return demod_batch_locked(c, mode, reinterpret_cast<const float2*>(d_iq), n_packets, samples_per_packet,
+                              packet_stride, d_symbols, symbol_stride, d_peaks, d_metrics,
+                              static_cast<cudaStream_t>(stream));
+}
+
+static int estimate_batch_locked(lora_b200_ctx* c, const float2* d_iq, size_t n_packets, size_t count,
+                                 size_t packet_stride, lora_b200_pkt_metrics* d_metrics, cudaStream_t st)
+{
+    const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
+    if (!d_iq || !d_metrics) return fail(LORA_B200_EINVAL, "null buffer");
+    const size_t symbols = count / step; // phy.cpp:86-87: every whole symbol offered is used
+    if (n_packets == 0 || symbols == 0) return LORA_B200_OK; // :83,88 silently return
+    if (symbols > 0x7fffffff) return fail(LORA_B200_EINVAL, "too many symbols");
+    CU(c->est.reserve(sizeof(float4) * n_packets));
+    CU(c->sync_raw.reserve(sizeof(uint16_t) * 2 * n_packets));
+    const int np = static_cast<int>(n_packets);
+    CU(launch_fill_est(c->est.as<float4>(), np, st));
+    EstimateArgs ea{};
+    ea.iq = d_iq; ea.packet_stride = packet_stride;
+    ea.symbols = static_cast<int>(symbols);
+    ea.osr = static_cast<int>(c->cfg.osr);
+    ea.tw = c->d_tw; ea.down = c->d_down; ea.window = c->d_window;
+    ea.power_scale = c->power_scale;
+    ea.est = c->est.as<float4>();
+    CU(launch_estimate(static_cast<int>(c->cfg.sf), ea, np, st));
+    FinalizeArgs fa{c->est.as<float4>(), c->sync_raw.as<uint16_t>(), d_metrics, np, static_cast<int>(c->cfg.sf), 0, 0, 0};
+    CU(launch_finalize(fa, st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_estimate_batch(lora_b200_ctx* c, const lora_b200_c32* d_iq, size_t n_packets,
+                                        size_t samples_per_packet, size_t packet_stride,
+                                        lora_b200_pkt_metrics* d_metrics, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return estimate_batch_locked(c, reinterpret_cast<const float2*>(d_iq), n_packets, samples_per_packet,
+                                 packet_stride, d_metrics, static_cast<cudaStream_t>(stream));
+}
+
+// ---- integer back end ------------------------------------------------------------------------------------
+static int check_chain_cfg(const lora_b200_chain_cfg* g)
+{
+    if (!g) return fail(LORA_B200_EINVAL, "null chain config");
+    const unsigned ppm = g->ppm ? g->ppm : g->sf;
+    if (g->sf < 5 || g->sf > 12) return fail(LORA_B200_EINVAL, "chain sf must be 5..12");
+    if (ppm > g->sf) return fail(LORA_B200_EINVAL, "failed check: PPM <= SF (LoRaDecoder.cpp:202)");
+    if (ppm < 5) return fail(LORA_B200_EINVAL, "ppm must be >= 5 (the header needs 5 codewords)");
+    if (g->rdd > 4) return fail(LORA_B200_EINVAL, "unknown coding rate (LoRaDecoder.cpp:143-151)");
+    if (g->data_length > 255) return fail(LORA_B200_EINVAL, "data_length > 255");
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_decode_batch(lora_b200_ctx* c, const uint16_t* d_symbols, size_t n_packets,
+                                      size_t symbols_per_packet, size_t symbol_stride, uint8_t* d_bytes,
+                                      size_t byte_stride, uint8_t* d_crc_ok, void* stream)
+{
+    if (!c || !d_symbols || !d_bytes) return fail(LORA_B200_EINVAL, "null argument"); // phy.cpp:244
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || symbol_stride < symbols_per_packet || byte_stride < symbols_per_packet / 2)
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    SimpleDecodeArgs a{d_symbols, symbols_per_packet, symbol_stride, d_bytes, byte_stride, d_crc_ok,
+                       static_cast<int>(n_packets)};
+    CU(launch_simple_decode(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_encode_batch(lora_b200_ctx* c, const uint8_t* d_bytes, size_t n_packets,
+                                      size_t bytes_per_packet, size_t byte_stride, uint16_t* d_symbols,
+                                      size_t symbol_stride, void* stream)
+{
+    if (!c || !d_bytes || !d_symbols) return fail(LORA_B200_EINVAL, "null argument"); // phy.cpp:58
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || byte_stride < bytes_per_packet || symbol_stride < 2 * bytes_per_packet)
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    SimpleEncodeArgs a{d_bytes, bytes_per_packet, byte_stride, d_symbols, symbol_stride, static_cast<int>(n_packets)};
+    CU(launch_simple_encode(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+static int chain_decode_locked(lora_b200_ctx* c, const lora_b200_chain_cfg* g, const uint16_t* d_symbols,
+                               size_t n_packets, size_t nsym, size_t symbol_stride, uint8_t* d_payload,
+                               lora_b200_chain_result* d_results, cudaStream_t st)
+{
+    if (int rc = check_chain_cfg(g)) return rc;
+    if (!d_symbols || !d_payload || !d_results) return fail(LORA_B200_EINVAL, "null buffer");
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || symbol_stride < nsym || nsym > 0xffff)
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    ChainDecodeArgs a{*g, d_symbols, nsym, symbol_stride, d_payload, d_results, c->d_whiten, static_cast<int>(n_packets)};
+    CU(launch_chain_decode(a, st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_chain_decode_batch(lora_b200_ctx* c, const lora_b200_chain_cfg* g,
+                                            const uint16_t* d_symbols, size_t n_packets, size_t nsym,
+                                            size_t symbol_stride, uint8_t* d_payload,
+                                            lora_b200_chain_result* d_results, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return chain_decode_locked(c, g, d_symbols, n_packets, nsym, symbol_stride, d_payload, d_results,
+                               static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int lora_b200_chain_encode_batch(lora_b200_ctx* c, const lora_b200_chain_cfg* g,
+                                            const uint8_t* d_payload, size_t n_packets, size_t payload_len,
+                                            size_t payload_stride, uint16_t* d_symbols, size_t symbol_stride,
+                                            size_t* symbols_per_packet, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (int rc = check_chain_cfg(g)) return rc;
+    if (payload_len > 255) return fail(LORA_B200_EINVAL, "payload longer than 255 bytes");
+    const size_t nsym = chain_symbol_count(*g, payload_len);
+    if (nsym == 0) return fail(LORA_B200_EINVAL, "invalid chain configuration");
+    if (symbols_per_packet) *symbols_per_packet = nsym;
+    if (!d_symbols) return LORA_B200_OK; // size query
+    if (!d_payload && payload_len) return fail(LORA_B200_EINVAL, "null payload");
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || symbol_stride < nsym || payload_stride < payload_len)
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    ChainEncodeArgs a{*g, d_payload, payload_len, payload_stride, d_symbols, symbol_stride, c->d_whiten,
+                      static_cast<int>(n_packets)};
+    CU(launch_chain_encode(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+// ---- transmit side --------------------------------------------------------------------------------------
+static int modulate_locked(lora_b200_ctx* c, const uint16_t* d_symbols, size_t n_packets, size_t nsym,
+                           size_t symbol_stride, float amplitude, uint8_t sync, float2* d_iq,
+                           size_t packet_stride, cudaStream_t st)
+{
+    if (!d_iq || (!d_symbols && nsym)) return fail(LORA_B200_EINVAL, "null buffer");
+    if (n_packets == 0) return LORA_B200_OK;
+    const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
+    if (n_packets > 0x7fffffffu || packet_stride < (nsym + 2) * step || (nsym && symbol_stride < nsym))
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    ModulateArgs a{};
+    a.symbols = d_symbols; a.n_symbols = nsym; a.symbol_stride = symbol_stride;
+    a.iq = d_iq; a.packet_stride = packet_stride;
+    a.n_packets = static_cast<int>(n_packets);
+    a.sf = static_cast<int>(c->cfg.sf); a.osr = static_cast<int>(c->cfg.osr);
+    a.bw_scale = c->bw_scale;
+    a.amplitude = std::fmax(-1.0f, std::fmin(1.0f, amplitude)); // LoRaMod.cpp:18
+    const unsigned shift = c->cfg.sf > 4 ? c->cfg.sf - 4 : 0;   // :20-22
+    a.sw0 = static_cast<uint16_t>((sync >> 4) << shift);
+    a.sw1 = static_cast<uint16_t>((sync & 0x0f) << shift);
+    CU(launch_modulate(a, st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_modulate_batch(lora_b200_ctx* c, const uint16_t* d_symbols, size_t n_packets,
+                                        size_t symbols_per_packet, size_t symbol_stride, float amplitude,
+                                        uint8_t sync, lora_b200_c32* d_iq, size_t packet_stride, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return modulate_locked(c, d_symbols, n_packets, symbols_per_packet, symbol_stride, amplitude, sync,
+                           reinterpret_cast<float2*>(d_iq), packet_stride, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int lora_b200_awgn_batch(lora_b200_ctx* c, lora_b200_c32* d_iq, size_t n_packets,
+                                    size_t samples_per_packet, size_t packet_stride, const float* d_snr_db,
+                                    uint64_t seed, void* stream)
+{
+    if (!c || !d_iq || !d_snr_db) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_packets == 0 || samples_per_packet == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || packet_stride < samples_per_packet) return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    AwgnArgs a{reinterpret_cast<float2*>(d_iq), samples_per_packet, packet_stride, d_snr_db, seed, static_cast<int>(n_packets)};
+    CU(launch_awgn(a, c->sm_count, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+// ---- host-buffer entry points -----------------------------------------------------------------------------
+extern "C" int lora_b200_demodulate_host(lora_b200_ctx* c, int mode, const lora_b200_c32* h_iq, size_t count,
+                                         uint16_t* h_symbols, size_t symbol_cap, size_t* n_symbols,
+                                         lora_b200_pkt_metrics* h_metrics)
+{
+    if (!c || !h_iq || !h_symbols) return fail(LORA_B200_EINVAL, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
+    const size_t total = count / step;
+    const size_t n_out = total >= 2 ? total - 2 : total;
+    if (mode == LORA_B200_DEMOD_WORKSPACE && n_out > symbol_cap && total >= 2 && count % step == 0)
+        return fail(LORA_B200_EINVAL, "symbol buffer too small"); // phy.cpp:190
+    if (n_symbols) *n_symbols = 0;
+    if (count == 0) return mode == LORA_B200_DEMOD_WORKSPACE ? fail(LORA_B200_EINVAL, "no samples") : LORA_B200_OK;
+    CU(c->s_iq.reserve(sizeof(float2) * count));
+    CU(c->s_sym.reserve(sizeof(uint16_t) * (n_out + 1)));
+    CU(c->s_metrics.reserve(sizeof(lora_b200_pkt_metrics)));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count, cudaMemcpyHostToDevice, st));
+    int rc = demod_batch_locked(c, mode, c->s_iq.as<float2>(), 1, count, count, c->s_sym.as<uint16_t>(), n_out + 1,
+                                nullptr, c->s_metrics.as<lora_b200_pkt_metrics>(), st);
+    if (rc) return rc;
+    lora_b200_pkt_metrics m{};
+    CU(cudaMemcpyAsync(&m, c->s_metrics.p, sizeof(m), cudaMemcpyDeviceToHost, st));
+    const size_t ncopy = n_out < symbol_cap ? n_out : symbol_cap;
+    if (ncopy) CU(cudaMemcpyAsync(h_symbols, c->s_sym.p, sizeof(uint16_t) * ncopy, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (total == 0) { m.cfo = NAN; m.time_offset = NAN; } // 0/0 in LoRaDemod.cpp:125
+    if (h_metrics) *h_metrics = m;
+    if (n_symbols) *n_symbols = n_out;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_estimate_host(lora_b200_ctx* c, const lora_b200_c32* h_iq, size_t count, float* cfo,
+                                       float* time_offset)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (!h_iq || count == 0) return LORA_B200_OK; // phy.cpp:83: silently returns
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
+    if (count / step == 0) return LORA_B200_OK;
+    CU(c->s_iq.reserve(sizeof(float2) * count));
+    CU(c->s_metrics.reserve(sizeof(lora_b200_pkt_metrics)));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count, cudaMemcpyHostToDevice, st));
+    int rc = estimate_batch_locked(c, c->s_iq.as<float2>(), 1, count, count, c->s_metrics.as<lora_b200_pkt_metrics>(), st);
+    if (rc) return rc;
+    lora_b200_pkt_metrics m{};
+    CU(cudaMemcpyAsync(&m, c->s_metrics.p, sizeof(m), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (cfo) *cfo = m.cfo;
+    if (time_offset) *time_offset = m.time_offset;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_modulate_host(lora_b200_ctx* c, const uint16_t* h_symbols, size_t nsym, float amplitude,
+                                       uint8_t sync, lora_b200_c32* h_iq, size_t iq_cap, size_t* n_samples)
+{
+    if (!c || !h_iq || (!h_symbols && nsym)) return fail(LORA_B200_EINVAL, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const size_t produced = (nsym + 2) * static_cast<size_t>(c->n) * c->cfg.osr;
+    if (n_samples) *n_samples = produced;
+    if (produced > iq_cap) return fail(LORA_B200_EINVAL, "iq buffer too small"); // phy.cpp:74
+    CU(c->s_iq.reserve(sizeof(float2) * produced));
+    CU(c->s_sym.reserve(sizeof(uint16_t) * (nsym + 1)));
+    cudaStream_t st = c->stream;
+    if (nsym) CU(cudaMemcpyAsync(c->s_sym.p, h_symbols, sizeof(uint16_t) * nsym, cudaMemcpyHostToDevice, st));
+    int rc = modulate_locked(c, c->s_sym.as<uint16_t>(), 1, nsym, nsym + 1, amplitude, sync, c->s_iq.as<float2>(), produced, st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(h_iq, c->s_iq.p, sizeof(float2) * produced, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_receive_host(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
+                                      const lora_b200_c32* h_iq, size_t n_packets, size_t count,
+                                      uint8_t* h_payload, lora_b200_chain_result* h_results,
+                                      lora_b200_pkt_metrics* h_metrics)
+{
+    if (!c || !h_iq || !h_payload || !h_results) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_packets == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
+    const size_t total = count / step;
+    if (total < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
+    const size_t nsym = total - 2;
+    CU(c->s_iq.reserve(sizeof(float2) * count * n_packets));
+    CU(c->s_sym.reserve(sizeof(uint16_t) * nsym * n_packets + 2));
+    CU(c->s_metrics.reserve(sizeof(lora_b200_pkt_metrics) * n_packets));
+    CU(c->s_payload.reserve(static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * n_packets));
+    CU(c->s_results.reserve(sizeof(lora_b200_chain_result) * n_packets));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count * n_packets, cudaMemcpyHostToDevice, st));
+    int rc = demod_batch_locked(c, mode, c->s_iq.as<float2>(), n_packets, count, count, c->s_sym.as<uint16_t>(), nsym,
+                                nullptr, c->s_metrics.as<lora_b200_pkt_metrics>(), st);
+    if (rc) return rc;
+    rc = chain_decode_locked(c, g, c->s_sym.as<uint16_t>(), n_packets, nsym, nsym, c->s_payload.as<uint8_t>(),
+                             c->s_results.as<lora_b200_chain_result>(), st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(h_payload, c->s_payload.p, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * n_packets, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h_results, c->s_results.p, sizeof(lora_b200_chain_result) * n_packets, cudaMemcpyDeviceToHost, st));
+    if (h_metrics)
+        CU(cudaMemcpyAsync(h_metrics, c->s_metrics.p, sizeof(lora_b200_pkt_metrics) * n_packets, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return LORA_B200_OK;
+}

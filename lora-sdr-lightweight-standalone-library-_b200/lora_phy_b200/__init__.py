@@ -1,0 +1,294 @@
+"""lora_phy_b200 -- Python host layer over the C ABI of liblora_phy_b200.so (include/lora_phy_b200.h).
+
+Nothing here computes: every method forwards to a CUDA entry point.  torch is used only to own device
+memory and streams.  There is no CPU fallback -- if the shared library or a CUDA device is missing,
+loading or context creation raises.
+
+The method names follow the reference API they stand in for (include/lora_phy/phy.hpp:102-215):
+`demodulate`, `lora_demodulate`, `estimate_offsets`, `decode`, `lora_encode`, `lora_modulate`, plus the
+full coding chain of LoRa-SDR/LoRaEncoder.cpp / LoRaDecoder.cpp as `chain_encode` / `chain_decode`.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "liblora_phy_b200.so")
+
+DEMOD_WORKSPACE, DEMOD_LEGACY, DEMOD_LEGACY_DECHIRP = 0, 1, 2
+PAYLOAD_STRIDE = 264
+
+
+class Config(C.Structure):
+    _fields_ = [("sf", C.c_uint), ("bw_hz", C.c_uint), ("osr", C.c_uint), ("window", C.c_int),
+                ("device", C.c_int)]
+
+
+class ChainCfg(C.Structure):
+    _fields_ = [("sf", C.c_uint), ("ppm", C.c_uint), ("rdd", C.c_uint), ("explicit_header", C.c_int),
+                ("crc", C.c_int), ("whitening", C.c_int), ("interleaving", C.c_int),
+                ("error_check", C.c_int), ("hdr_out", C.c_int), ("data_length", C.c_uint)]
+
+
+PKT_METRICS = np.dtype([("cfo", "<f4"), ("time_offset", "<f4"), ("max_amp", "<f4"), ("sync_word", "u1"),
+                        ("normalised", "u1"), ("n_symbols", "<u2")])
+CHAIN_RESULT = np.dtype([("n_bytes", "<i2"), ("drop_line", "<i2"), ("parity_error", "u1"),
+                         ("uncorrectable", "u1"), ("hdr_length", "u1"), ("hdr_has_crc", "u1"),
+                         ("hdr_rdd", "u1"), ("hdr_checksum", "u1"), ("crc_present", "u1"), ("crc_ok", "u1"),
+                         ("reserved", "u1", 4)])
+assert PKT_METRICS.itemsize == 16 and CHAIN_RESULT.itemsize == 16
+
+
+class LoraB200Error(RuntimeError):
+    pass
+
+
+def chain_cfg(sf, rdd, ppm=0, explicit=True, crc=True, whitening=True, interleaving=True,
+              error_check=False, hdr_out=False, data_length=8):
+    return ChainCfg(sf, ppm, rdd, int(explicit), int(crc), int(whitening), int(interleaving),
+                    int(error_check), int(hdr_out), data_length)
+
+
+_lib = None
+
+_SIGNATURES = {
+    "lora_b200_ctx_create": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p)]),
+    "lora_b200_ctx_destroy": (None, [C.c_void_p]),
+    "lora_b200_last_error": (C.c_char_p, []),
+    "lora_b200_launch_count": (C.c_ulonglong, []),
+    "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
+    "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                        C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_estimate_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                           C.c_void_p, C.c_void_p]),
+    "lora_b200_decode_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
+    "lora_b200_chain_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
+                                               C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_encode_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                         C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lora_b200_chain_encode_batch": (C.c_int, [C.c_void_p, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
+                                               C.c_size_t, C.c_size_t, C.c_void_p, C.c_size_t,
+                                               C.POINTER(C.c_size_t), C.c_void_p]),
+    "lora_b200_modulate_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                           C.c_float, C.c_uint8, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lora_b200_awgn_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                       C.c_void_p, C.c_uint64, C.c_void_p]),
+    "lora_b200_demodulate_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p,
+                                            C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p]),
+    "lora_b200_estimate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float),
+                                          C.POINTER(C.c_float)]),
+    "lora_b200_modulate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_uint8,
+                                          C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "lora_b200_receive_host": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
+                                         C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+EXPORTS = tuple(_SIGNATURES)
+
+
+def load_library():
+    """Load liblora_phy_b200.so (built in tree by __graft_entry__.build / make).  Raises if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise LoraB200Error(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
+                                "g.build()'`; there is no CPU fallback")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            f = getattr(lib, name)
+            f.restype, f.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def launch_count():
+    return int(load_library().lora_b200_launch_count())
+
+
+def _check(rc):
+    if rc != 0:
+        raise LoraB200Error(f"lora_b200 error {rc}: {load_library().lora_b200_last_error().decode()}")
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Context:
+    """One (sf, bw, osr, window) configuration on one GPU; owns the uploaded tables."""
+
+    def __init__(self, sf, bw_hz=125000, osr=1, window=False, device=-1):
+        self.lib = load_library()
+        self.sf, self.bw_hz, self.osr, self.window = sf, bw_hz, max(osr, 1), bool(window)
+        self.n = 1 << sf
+        self.step = self.n * self.osr
+        cfg = Config(sf, bw_hz, osr, int(bool(window)), device)
+        h = C.c_void_p()
+        _check(self.lib.lora_b200_ctx_create(C.byref(cfg), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lora_b200_ctx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def table(self, which):
+        out = np.zeros(self.n, np.float32 if which == 2 else np.complex64)
+        _check(self.lib.lora_b200_ctx_table(self.h, which, out.ctypes.data_as(C.c_void_p), self.n))
+        return out
+
+    # ---- device-tensor batch API ------------------------------------------------------------------
+    def demod_batch(self, iq, mode=DEMOD_WORKSPACE, want_peaks=False, symbols=None, metrics=None, peaks=None):
+        """iq: CUDA complex64 tensor [n_packets, samples].  -> (symbols u16 [n, total-2], metrics, peaks)."""
+        import torch
+        assert iq.is_cuda and iq.dtype == torch.complex64 and iq.dim() == 2 and iq.stride(1) == 1
+        n, count = iq.shape
+        total = count // self.step
+        n_out = total - 2 if total >= 2 else total
+        if symbols is None:
+            symbols = torch.zeros((n, max(n_out, 1)), dtype=torch.int16, device=iq.device)
+        if metrics is None:
+            metrics = torch.zeros((n, 16), dtype=torch.uint8, device=iq.device)
+        if want_peaks and peaks is None:
+            peaks = torch.zeros((n, max(total, 1)), dtype=torch.float32, device=iq.device)
+        _check(self.lib.lora_b200_demod_batch(self.h, mode, _ptr(iq), n, count, iq.stride(0), _ptr(symbols),
+                                              symbols.stride(0), _ptr(peaks), _ptr(metrics), _stream()))
+        return symbols[:, :n_out], metrics, peaks
+
+    def estimate_batch(self, iq):
+        import torch
+        n, count = iq.shape
+        metrics = torch.zeros((n, 16), dtype=torch.uint8, device=iq.device)
+        _check(self.lib.lora_b200_estimate_batch(self.h, _ptr(iq), n, count, iq.stride(0), _ptr(metrics), _stream()))
+        return metrics
+
+    def decode_batch(self, symbols):
+        """lora_decode + CRC flag.  symbols: CUDA int16 [n, nsym] -> (bytes u8 [n, nsym//2], crc_ok u8 [n])."""
+        import torch
+        n, nsym = symbols.shape
+        out = torch.zeros((n, max(nsym // 2, 1)), dtype=torch.uint8, device=symbols.device)
+        ok = torch.zeros(n, dtype=torch.uint8, device=symbols.device)
+        _check(self.lib.lora_b200_decode_batch(self.h, _ptr(symbols), n, nsym, symbols.stride(0), _ptr(out),
+                                               out.stride(0), _ptr(ok), _stream()))
+        return out[:, : nsym // 2], ok
+
+    def encode_batch(self, data):
+        import torch
+        n, nb = data.shape
+        sym = torch.zeros((n, max(2 * nb, 1)), dtype=torch.int16, device=data.device)
+        _check(self.lib.lora_b200_encode_batch(self.h, _ptr(data), n, nb, data.stride(0), _ptr(sym),
+                                               sym.stride(0), _stream()))
+        return sym[:, : 2 * nb]
+
+    def chain_decode_batch(self, cfg, symbols, payload=None, results=None):
+        import torch
+        n, nsym = symbols.shape
+        if payload is None:
+            payload = torch.zeros((n, PAYLOAD_STRIDE), dtype=torch.uint8, device=symbols.device)
+        if results is None:
+            results = torch.zeros((n, 16), dtype=torch.uint8, device=symbols.device)
+        _check(self.lib.lora_b200_chain_decode_batch(self.h, C.byref(cfg), _ptr(symbols), n, nsym,
+                                                     symbols.stride(0), _ptr(payload), _ptr(results), _stream()))
+        return payload, results
+
+    def chain_symbol_count(self, cfg, payload_len):
+        k = C.c_size_t()
+        _check(self.lib.lora_b200_chain_encode_batch(self.h, C.byref(cfg), None, 0, payload_len, payload_len,
+                                                     None, 0, C.byref(k), None))
+        return k.value
+
+    def chain_encode_batch(self, cfg, payload):
+        import torch
+        n, plen = payload.shape
+        nsym = self.chain_symbol_count(cfg, plen)
+        sym = torch.zeros((n, nsym), dtype=torch.int16, device=payload.device)
+        k = C.c_size_t()
+        _check(self.lib.lora_b200_chain_encode_batch(self.h, C.byref(cfg), _ptr(payload), n, plen,
+                                                     payload.stride(0), _ptr(sym), sym.stride(0), C.byref(k), _stream()))
+        return sym
+
+    def modulate_batch(self, symbols, amplitude=1.0, sync=0x12, out=None):
+        import torch
+        n, nsym = symbols.shape
+        count = (nsym + 2) * self.step
+        if out is None:
+            out = torch.zeros((n, count), dtype=torch.complex64, device=symbols.device)
+        _check(self.lib.lora_b200_modulate_batch(self.h, _ptr(symbols), n, nsym, symbols.stride(0), amplitude,
+                                                 sync, _ptr(out), out.stride(0), _stream()))
+        return out
+
+    def awgn_batch(self, iq, snr_db, seed=0):
+        n, count = iq.shape
+        _check(self.lib.lora_b200_awgn_batch(self.h, _ptr(iq), n, count, iq.stride(0), _ptr(snr_db), seed, _stream()))
+        return iq
+
+    # ---- host-buffer API (what include/lora_phy/phy.hpp forwards to) ------------------------------------
+    def _demod_host(self, mode, iq):
+        iq = np.ascontiguousarray(iq, np.complex64)
+        total = len(iq) // self.step
+        sym = np.zeros(max(total, 1), np.uint16)
+        m = np.zeros(1, PKT_METRICS)
+        k = C.c_size_t()
+        rc = self.lib.lora_b200_demodulate_host(self.h, mode, iq.ctypes.data_as(C.c_void_p), len(iq),
+                                                sym.ctypes.data_as(C.c_void_p), len(sym), C.byref(k),
+                                                m.ctypes.data_as(C.c_void_p))
+        return rc, sym[: k.value], m[0]
+
+    def demodulate(self, iq):
+        """lora_phy::demodulate (phy.cpp:178-239): -> (ret, symbols, metrics); ret = -1 on the reference's guards."""
+        rc, sym, m = self._demod_host(DEMOD_WORKSPACE, iq)
+        if rc == -1:
+            return -1, sym[:0], m
+        _check(rc)
+        return len(sym), sym, m
+
+    def lora_demodulate(self, samples, dechirp=False, scratch=True):
+        """lora_phy::lora_demodulate (LoRaDemod.cpp:49-195): -> (ret, symbols, sync, metrics).
+        dechirp=True fuses the caller-side dechirp of tests/e2e_chain_test.cpp:79-93 in front."""
+        rc, sym, m = self._demod_host(DEMOD_LEGACY_DECHIRP if dechirp else DEMOD_LEGACY, samples)
+        _check(rc)
+        if m["normalised"] and not scratch:  # LoRaDemod.cpp:69-71: no scratch buffer -> 0 symbols
+            return 0, sym[:0], 0, m
+        total = len(samples) // self.step
+        return (len(sym) if total >= 2 else total), sym, int(m["sync_word"]), m
+
+    def estimate_offsets(self, samples):
+        samples = np.ascontiguousarray(samples, np.complex64)
+        cfo, to = C.c_float(0), C.c_float(0)
+        _check(self.lib.lora_b200_estimate_host(self.h, samples.ctypes.data_as(C.c_void_p), len(samples),
+                                                C.byref(cfo), C.byref(to)))
+        return np.float32(cfo.value), np.float32(to.value)
+
+    def lora_modulate(self, symbols, amplitude=1.0, sync=0x12):
+        symbols = np.ascontiguousarray(symbols, np.uint16)
+        out = np.zeros((len(symbols) + 2) * self.step, np.complex64)
+        k = C.c_size_t()
+        _check(self.lib.lora_b200_modulate_host(self.h, symbols.ctypes.data_as(C.c_void_p) if len(symbols) else None,
+                                                len(symbols), amplitude, sync, out.ctypes.data_as(C.c_void_p),
+                                                len(out), C.byref(k)))
+        return out[: k.value]
+
+    def receive_host(self, cfg, iq, mode=DEMOD_LEGACY_DECHIRP, payload=None, results=None, metrics=None):
+        """Host IQ [n, samples] -> (payload u8 [n, 264], results, metrics): demod + chain decode end to end."""
+        iq = np.ascontiguousarray(iq, np.complex64)
+        n, count = iq.shape
+        payload = np.zeros((n, PAYLOAD_STRIDE), np.uint8) if payload is None else payload
+        results = np.zeros(n, CHAIN_RESULT) if results is None else results
+        metrics = np.zeros(n, PKT_METRICS) if metrics is None else metrics
+        _check(self.lib.lora_b200_receive_host(self.h, mode, C.byref(cfg), iq.ctypes.data_as(C.c_void_p), n, count,
+                                               payload.ctypes.data_as(C.c_void_p), results.ctypes.data_as(C.c_void_p),
+                                               metrics.ctypes.data_as(C.c_void_p)))
+        return payload, results, metrics
+
+
+def metrics_to_numpy(t):
+    """CUDA uint8 [n,16] metrics / results tensor -> structured numpy array (pass dtype via .view)."""
+    return t.cpu().numpy()
