@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on its configs[1]: the SF7..SF12 sweep, 65,536 synthetic AWGN packets
+per SF (SNR -20..+10 dB), demodulation + full decode.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--packets P] [--impl reference]
+
+One "step" = one pass of the receive hot path over the whole sweep (six batches, one per SF): max-abs
+prepass + offset estimate + fused dechirp/FFT/argmax + chain decode, with the reference's
+`caller dechirp -> lora_demodulate` semantics (the pipeline its own tests/performance_test.cpp times), so
+packets really decode.  Inputs are resident in HBM when the timed region starts; `e2e` repeats the same
+metric through the host-buffer C-ABI call with the copies inside the timed region.  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, "lora-sdr-lightweight-standalone-library-_b200"), os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+SFS = (7, 8, 9, 10, 11, 12)
+PAYLOAD_LEN = 16           # bytes, uniform random
+RDD = 1                    # CR 4/5, explicit header, CRC on
+SNRS = (-20.0, -15.0, -10.0, -5.0, 0.0, 5.0, 10.0)
+METRIC = "decoded Msamples/s (SF7-SF12 sweep, demod + full decode)"
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+def symbols_per_packet(sf):
+    """LoRaEncoder.cpp:174-175 for a 16-byte payload + CRC, explicit header, CR 4/5, ppm = sf."""
+    ncw = -(-((PAYLOAD_LEN + 2) * 2 + 5) // sf) * sf
+    return 8 + (ncw // sf - 1) * (4 + RDD)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+class Workload:
+    """Device-resident synthetic input for one rank: per SF, `packets` packets built with the library's own
+    encoder -> modulator -> AWGN kernels (seeded; nothing is read from disk)."""
+
+    def __init__(self, L, torch, packets, rank, sfs=SFS):
+        self.L, self.torch = L, torch
+        self.items = []
+        for sf in sfs:
+            ctx = L.Context(sf)
+            cfg = L.chain_cfg(sf, RDD)
+            gen = torch.Generator(device="cuda").manual_seed(1 + sf + 1000 * rank)  # mt19937 seed 1 analogue
+            pay = torch.randint(0, 256, (packets, PAYLOAD_LEN), dtype=torch.uint8, device="cuda", generator=gen)
+            sym = ctx.chain_encode_batch(cfg, pay)
+            assert sym.shape[1] == symbols_per_packet(sf)
+            iq = ctx.modulate_batch(sym)
+            pick = torch.randint(0, len(SNRS), (packets,), device="cuda", generator=gen)
+            snr = torch.tensor(SNRS, dtype=torch.float32, device="cuda")[pick]
+            ctx.awgn_batch(iq, snr, seed=sf + 100 * rank)
+            n, nsym = packets, sym.shape[1]
+            self.items.append(dict(
+                sf=sf, ctx=ctx, cfg=cfg, iq=iq, payload=pay, tx=sym, snr=snr,
+                rx=torch.zeros((n, nsym), dtype=torch.int16, device="cuda"),
+                metrics=torch.zeros((n, 16), dtype=torch.uint8, device="cuda"),
+                out=torch.zeros((n, L.PAYLOAD_STRIDE), dtype=torch.uint8, device="cuda"),
+                results=torch.zeros((n, 16), dtype=torch.uint8, device="cuda"),
+                windows=n * (nsym + 2), samples=n * (nsym + 2) * (1 << sf)))
+        torch.cuda.synchronize()
+        self.samples = sum(i["samples"] for i in self.items)
+        self.windows = sum(i["windows"] for i in self.items)
+        self.data_symbols = sum(i["rx"].numel() for i in self.items)
+
+    def step(self, mode):
+        for i in self.items:
+            i["ctx"].demod_batch(i["iq"], mode=mode, symbols=i["rx"], metrics=i["metrics"])
+            i["ctx"].chain_decode_batch(i["cfg"], i["rx"], payload=i["out"], results=i["results"])
+
+    def set_timing(self, on):
+        for i in self.items:
+            i["ctx"].set_kernel_timing(on)
+
+    def kernel_time(self):
+        per_sf, tot_ms, tot_k = {}, 0.0, 0
+        for i in self.items:
+            ms, k = i["ctx"].kernel_time()
+            per_sf[i["sf"]] = (ms, k)
+            tot_ms += ms; tot_k += k
+        return tot_ms, tot_k, per_sf
+
+
+# ---- the reference's CPU path, timed on the host cores ---------------------------------------------------
+def cpu_reference_time(host_items, threads):
+    """host_items: [(sf, iq complex64 [P, count], nsym)].  Runs the reference pipeline
+    caller-dechirp -> lora_demodulate (tests/performance_test.cpp:109-116) on every packet with oracle/_ref
+    (the unmodified reference, kind "reference") or, where that was never built, the C restatement (kind
+    "port"), plus the restated chain decode; `threads` host threads, one workspace each (ctypes releases
+    the GIL).  -> (seconds, samples, kind)."""
+    import ctypes as C
+    from concurrent.futures import ThreadPoolExecutor
+    from _oracle import ORC, REF, Metrics, chain_cfg as orc_cfg, c64p, u16p
+
+    kind = "reference" if REF is not None else "port"
+    tasks = []
+    for sf, iq, nsym in host_items:
+        chunk = max(1, len(iq) // (threads * 4))
+        for a in range(0, len(iq), chunk):
+            tasks.append((sf, iq, nsym, a, min(len(iq), a + chunk)))
+
+    if REF is not None:
+        create = REF.fn("legacy_create", C.c_void_p, [C.c_uint, C.c_int, C.c_size_t, C.c_uint])
+        destroy = REF.fn("legacy_destroy", None, [C.c_void_p])
+        run = REF.fn("legacy_dechirp_demodulate", C.c_size_t, [C.c_void_p, c64p, C.c_size_t, u16p,
+                                                               C.POINTER(C.c_uint8), C.POINTER(Metrics)])
+
+    def work(task):
+        sf, iq, nsym, a, b = task
+        count = iq.shape[1]
+        out = np.zeros(nsym + 2, np.uint16)
+        cfg = orc_cfg(sf, RDD)
+        ok = 0
+        if REF is not None:
+            h = create(sf, 0, count, 125000)
+            sync, m = C.c_uint8(), Metrics()
+            for p in range(a, b):
+                k = run(h, iq[p], count, out, C.byref(sync), C.byref(m))
+                ok += ORC.chain_decode(cfg, out[:k])[2].crc_ok
+            destroy(h)
+        else:
+            n = 1 << sf
+            down = ORC.gen_chirp(n, 1, n, 0.0, True, 1.0, 0.0, 1.0)[0]
+            for p in range(a, b):
+                x = iq[p].reshape(-1, n)
+                re = (x.real * down.real[None]).astype(np.float32) - (x.imag * down.imag[None]).astype(np.float32)
+                im = (x.real * down.imag[None]).astype(np.float32) + (x.imag * down.real[None]).astype(np.float32)
+                _, sym, _, _ = ORC.lora_demodulate(sf, (re + 1j * im).astype(np.complex64).reshape(-1))
+                ok += ORC.chain_decode(cfg, sym)[2].crc_ok
+        return ok
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        ok = sum(ex.map(work, tasks))
+    dt = time.perf_counter() - t0
+    samples = sum(iq.size for _, iq, _ in host_items)
+    return dt, samples, kind, ok
+
+
+def cpu_synth(packets, seed=0):
+    """CPU-side synthesis for the reference arm (none of this repo's kernels on that path): oracle chain
+    encoder, the reference's own lora_modulate where oracle/_ref exists, numpy AWGN."""
+    from _oracle import ORC, REF, chain_cfg as orc_cfg
+    mod = REF if REF is not None else ORC
+    rng = np.random.default_rng(seed)
+    items = []
+    for sf in SFS:
+        nsym = symbols_per_packet(sf)
+        iq = np.zeros((packets, (nsym + 2) << sf), np.complex64)
+        for p in range(packets):
+            sym = ORC.chain_encode(orc_cfg(sf, RDD), bytes(rng.integers(0, 256, PAYLOAD_LEN, dtype=np.uint8)))
+            clean = mod.lora_modulate(sym, sf)
+            sigma = 10.0 ** (-rng.choice(SNRS) / 20.0) / np.sqrt(2.0)
+            iq[p] = clean + (rng.standard_normal(len(clean)) + 1j * rng.standard_normal(len(clean))) * sigma
+        items.append((sf, iq, nsym))
+    return items
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    packets = args.ref_packets
+    items = cpu_synth(packets)
+    for _ in range(args.warmup):
+        cpu_reference_time(items, threads)
+    t, samples, kind = 0.0, 0, "port"
+    for _ in range(args.steps):
+        dt, s, kind, _ = cpu_reference_time(items, threads)
+        t += dt; samples += s
+    v = samples / t / 1e6
+    sample = f"{packets} packets per SF (SF7-12), {samples // args.steps} samples per step"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: SF7-SF12 sweep, AWGN -20..+10 dB, demod + full decode",
+                   "payload_bytes": PAYLOAD_LEN, "cr": "4/5", "header": "explicit", "crc": True, "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ---- this repo's arm ---------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--packets", type=int, default=65536, help="packets per SF per GPU")
+    ap.add_argument("--e2e-packets", type=int, default=2048)
+    ap.add_argument("--cpu-packets", type=int, default=512)
+    ap.add_argument("--ref-packets", type=int, default=128)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import lora_phy_b200 as L
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device; there is no CPU fallback"
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mode = L.DEMOD_LEGACY_DECHIRP if args.mode == "legacy_dechirp" else L.DEMOD_WORKSPACE
+
+    # size the batch to the HBM that is actually free (111.7 GB for 65,536 packets per SF)
+    free, _ = torch.cuda.mem_get_info()
+    per_packet = sum((symbols_per_packet(sf) + 2) * (1 << sf) * 8 + 1024 for sf in SFS)
+    packets = args.packets
+    while packets * per_packet > 0.85 * free and packets > 256:
+        packets //= 2
+    wl = Workload(L, torch, packets, rank)
+    gather_buf = None
+    res_cat = None
+    if dist is not None:
+        res_cat = torch.zeros((len(SFS) * packets, 16), dtype=torch.uint8, device="cuda")
+        gather_buf = torch.zeros((world * len(SFS) * packets, 16), dtype=torch.uint8, device="cuda")
+
+    def one_step():
+        wl.step(mode)
+        if dist is not None:  # the only NVLink traffic: the decoded-record gather
+            torch.cat([i["results"] for i in wl.items], out=res_cat)
+            dist.all_gather_into_tensor(gather_buf, res_cat)
+
+    for _ in range(args.warmup):
+        one_step()
+    torch.cuda.synchronize()
+    wl.set_timing(True)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    launches0 = L.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        one_step()
+    ev1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    clock_info = clocks.stop()
+    launches = L.launch_count() - launches0
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    k_ms, k_n, per_sf = wl.kernel_time()
+    wl.set_timing(False)
+
+    # sanity of what was decoded (not timed): CRC-ok rate and symbol agreement with what was sent
+    crc_ok, sym_ok = {}, {}
+    for i in wl.items:
+        r = i["results"].cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)
+        crc_ok[i["sf"]] = round(float((r["crc_ok"] == 1).mean()), 4)
+        sym_ok[i["sf"]] = round(float((i["rx"] == i["tx"]).float().mean().item()), 4)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    pk, pk_src = peaks()
+    samples_step = wl.samples * world
+    value = samples_step * args.steps / (ms_total * 1e-3) / 1e6
+    # roofline of the dominant kernel: 8*N*osr + 6 algorithmic bytes per window
+    alg_bytes = sum(i["windows"] * (8 * (1 << i["sf"]) + 6) for i in wl.items) * args.steps
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    per_sf_out = {}
+    for i in wl.items:
+        ms_sf, k_sf = per_sf[i["sf"]]
+        b = i["windows"] * (8 * (1 << i["sf"]) + 6) * max(k_sf, 1)
+        per_sf_out[str(i["sf"])] = {"kernel_ms": round(ms_sf / max(k_sf, 1), 4),
+                                    "GBps": round(b / (ms_sf * 1e-3) / 1e9, 1) if ms_sf > 0 else 0.0,
+                                    "Msamples_s": round(i["samples"] * max(k_sf, 1) / (ms_sf * 1e-3) / 1e6, 1) if ms_sf > 0 else 0.0,
+                                    "crc_ok": crc_ok[i["sf"]], "symbols_eq_tx": sym_ok[i["sf"]]}
+
+    # e2e: the same metric through the host-buffer C-ABI call, copies inside the timed region
+    e2e = None
+    cpu = None
+    if world == 1:
+        pe = min(args.e2e_packets, packets)
+        pinned = []
+        for i in wl.items:
+            h = torch.empty((pe, i["iq"].shape[1]), dtype=torch.complex64, pin_memory=True)
+            h.copy_(i["iq"][:pe])
+            pinned.append((i, h.numpy(), np.zeros((pe, L.PAYLOAD_STRIDE), np.uint8), np.zeros(pe, L.CHAIN_RESULT),
+                           np.zeros(pe, L.PKT_METRICS), h))
+        torch.cuda.synchronize()
+
+        def e2e_step():
+            for i, h_iq, pay, res, met, _ in pinned:
+                i["ctx"].receive_host(i["cfg"], h_iq, mode=mode, payload=pay, results=res, metrics=met)
+
+        for _ in range(2):
+            e2e_step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        dt = time.perf_counter() - t0
+        e_samples = sum(h.size for _, h, _, _, _, _ in pinned)
+        e2e = {"value": e_samples * args.steps / dt / 1e6, "unit": "Msamples/s",
+               "h2d_bytes_per_step": int(e_samples * 8),
+               "d2h_bytes_per_step": int(sum(p.nbytes + r.nbytes + m.nbytes for _, _, p, r, m, _ in pinned)),
+               "sample": f"{pe} packets per SF through lora_b200_receive_host, pinned host buffers"}
+        # same packets, the reference's CPU path on this box's host cores
+        pc = min(args.cpu_packets, pe)
+        threads = os.cpu_count() or 1
+        host_items = [(i["sf"], h_iq[:pc], i["tx"].shape[1]) for i, h_iq, _, _, _, _ in pinned]
+        dt_c, s_c, kind, _ = cpu_reference_time(host_items, threads)
+        cpu = {"value": s_c / dt_c / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
+               "sample": f"first {pc} packets per SF of the same workload ({s_c} samples, {dt_c:.1f} s wall)"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "msymbols_per_s": wl.data_symbols * world * args.steps / (ms_total * 1e-3) / 1e6,
+        "config": {"workload": "configs[1]: SF7-SF12 sweep, synthetic AWGN -20..+10 dB, demod + full decode",
+                   "packets_per_sf_per_gpu": packets, "payload_bytes": PAYLOAD_LEN, "cr": "4/5",
+                   "header": "explicit", "crc": True, "bw_hz": 125000, "osr": 1,
+                   "demod_semantics": args.mode, "parallelism": f"{world} independent shards, no data-path collective",
+                   "l2": "inputs (>= 2.3 GB per batch) are larger than the 126 MB L2; no flush needed",
+                   "per_sf": per_sf_out},
+        "clocks": clock_info, "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                     "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_src,
+                     "kernel": "demod_kernel<SF> (fused dechirp + rotate + FFT + argmax)",
+                     "kernel_ms_per_step": k_ms / args.steps, "kernel_launches": k_n},
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

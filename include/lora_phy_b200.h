@@ -100,6 +100,11 @@ void lora_b200_ctx_destroy(lora_b200_ctx* ctx);
 const char* lora_b200_last_error(void);
 /* Number of kernels this library has launched in this process (for bench.py's gpu_launches). */
 unsigned long long lora_b200_launch_count(void);
+/* Kernel timing for bench.py's roofline: when enabled, every launch of the fused dechirp+FFT+argmax kernel
+ * is bracketed by CUDA events on the stream it is launched on.  lora_b200_kernel_time synchronises those
+ * events, returns their summed duration and count since the last call, and resets the counters. */
+int lora_b200_set_kernel_timing(lora_b200_ctx* ctx, int enable);
+int lora_b200_kernel_time(lora_b200_ctx* ctx, double* total_ms, unsigned long long* launches);
 /* Copies of the host-built tables, for tests: table 0 twiddles, 1 down-chirp (n complex), 2 window (n floats). */
 int lora_b200_ctx_table(const lora_b200_ctx* ctx, int table, void* h_out, size_t n);
 

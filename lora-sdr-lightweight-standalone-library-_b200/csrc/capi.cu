@@ -76,6 +76,9 @@ struct lora_b200_ctx {
     Buf h_pin;                   // pinned bounce buffer
     cudaStream_t stream = nullptr;
     std::mutex mu;
+    bool timing = false;                                     // lora_b200_set_kernel_timing
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool; // reused event pairs
+    size_t ev_used = 0;
 };
 
 extern "C" const char* lora_b200_last_error(void) { return g_error.c_str(); }
@@ -138,8 +141,36 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
     for (Buf* b : {&c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
                    &c->s_misc, &c->h_pin})
         b->release();
+    for (auto& pr : c->ev_pool) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
+}
+
+extern "C" int lora_b200_set_kernel_timing(lora_b200_ctx* c, int enable)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->timing = enable != 0;
+    c->ev_used = 0;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_kernel_time(lora_b200_ctx* c, double* total_ms, unsigned long long* launches)
+{
+    if (!c || !total_ms || !launches) return fail(LORA_B200_EINVAL, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    double sum = 0.0;
+    for (size_t i = 0; i < c->ev_used; ++i) {
+        CU(cudaEventSynchronize(c->ev_pool[i].second));
+        float ms = 0.0f;
+        CU(cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second));
+        sum += ms;
+    }
+    *total_ms = sum;
+    *launches = c->ev_used;
+    c->ev_used = 0;
+    return LORA_B200_OK;
 }
 
 extern "C" int lora_b200_ctx_table(const lora_b200_ctx* c, int table, void* h_out, size_t n)
@@ -213,7 +244,21 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
         da.symbols = d_symbols; da.symbol_stride = symbol_stride;
         da.sync_raw = c->sync_raw.as<uint16_t>();
         da.peaks = d_peaks;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (c->timing) {
+            if (c->ev_used == c->ev_pool.size()) {
+                cudaEvent_t a = nullptr, b = nullptr;
+                CU(cudaEventCreate(&a));
+                CU(cudaEventCreate(&b));
+                c->ev_pool.emplace_back(a, b);
+            }
+            e0 = c->ev_pool[c->ev_used].first;
+            e1 = c->ev_pool[c->ev_used].second;
+            ++c->ev_used;
+            CU(cudaEventRecord(e0, st));
+        }
         CU(launch_demod(static_cast<int>(c->cfg.sf), da, c->sm_count, st));
+        if (e1) CU(cudaEventRecord(e1, st));
     }
     if (d_metrics) {
         FinalizeArgs fa{est, c->sync_raw.as<uint16_t>(), d_metrics, np, static_cast<int>(c->cfg.sf),

@@ -57,6 +57,8 @@ _SIGNATURES = {
     "lora_b200_ctx_destroy": (None, [C.c_void_p]),
     "lora_b200_last_error": (C.c_char_p, []),
     "lora_b200_launch_count": (C.c_ulonglong, []),
+    "lora_b200_set_kernel_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "lora_b200_kernel_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]),
     "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -139,6 +141,15 @@ class Context:
             self.h = None
 
     __del__ = close
+
+    def set_kernel_timing(self, enable):
+        _check(self.lib.lora_b200_set_kernel_timing(self.h, int(enable)))
+
+    def kernel_time(self):
+        """-> (summed ms, launches) of the fused demod kernel since the last call."""
+        ms, k = C.c_double(), C.c_ulonglong()
+        _check(self.lib.lora_b200_kernel_time(self.h, C.byref(ms), C.byref(k)))
+        return ms.value, int(k.value)
 
     def table(self, which):
         out = np.zeros(self.n, np.float32 if which == 2 else np.complex64)
