@@ -244,7 +244,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--packets", type=int, default=65536, help="packets per SF per GPU")
     ap.add_argument("--e2e-packets", type=int, default=2048)
-    ap.add_argument("--cpu-packets", type=int, default=512)
+    ap.add_argument("--cpu-packets", type=int, default=2048)
     ap.add_argument("--ref-packets", type=int, default=128)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace"])
@@ -372,9 +372,13 @@ def main():
         pc = min(args.cpu_packets, pe)
         threads = os.cpu_count() or 1
         host_items = [(i["sf"], h_iq[:pc], i["tx"].shape[1]) for i, h_iq, _, _, _, _ in pinned]
-        dt_c, s_c, kind, _ = cpu_reference_time(host_items, threads)
+        dt_c, s_c, kind, ok_cpu = cpu_reference_time(host_items, threads)
+        # live parity check: CRC-ok packets the CPU reference path finds in this sample vs what the GPU found
+        ok_gpu = int(sum((i["results"][:pc].cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)["crc_ok"] == 1).sum()
+                         for i in wl.items))
         cpu = {"value": s_c / dt_c / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
-               "sample": f"first {pc} packets per SF of the same workload ({s_c} samples, {dt_c:.1f} s wall)"}
+               "sample": f"first {pc} packets per SF of the same workload ({s_c} samples, {dt_c:.1f} s wall)",
+               "crc_ok_packets_cpu": int(ok_cpu), "crc_ok_packets_gpu_same_sample": ok_gpu}
 
     line = {
         "metric": METRIC, "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,

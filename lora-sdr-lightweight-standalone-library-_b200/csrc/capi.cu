@@ -237,6 +237,7 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
         da.total = static_cast<int>(total);
         da.osr = static_cast<int>(osr);
         da.dechirp = mode != LORA_B200_DEMOD_LEGACY;
+        da.dechirp_absolute = dechirp_in;
         da.use_scale = legacy;
         da.have_sync = have_sync;
         da.tw = c->d_tw; da.down = c->d_down; da.window = c->d_window;

@@ -187,8 +187,7 @@ struct CodewordCursor {
             for (int row = 0; row < rows; ++row) { // diagonalDeterleaveSx, LoRaCodes.hpp:396-412
                 unsigned v = gray_symbol(s_ofs + row);
                 for (int col = 0; col < ppm; ++col, v >>= 1) {
-                    int dst = col + row;
-                    if (dst >= ppm) dst -= ppm;
+                    const int dst = (col + row) % ppm; // row can exceed ppm (8 header rows, ppm >= 5)
                     cw[dst] |= (uint8_t)((v & 1u) << row);
                 }
             }
@@ -402,8 +401,7 @@ __global__ void chain_encode_kernel(ChainEncodeArgs a)
         for (int row = 0; row < rows; ++row) { // diagonalInterleaveSx, LoRaCodes.hpp:376-393
             unsigned v = 0;
             for (int col = 0; col < ppm; ++col) {
-                int src = col + row;
-                if (src >= ppm) src -= ppm;
+                const int src = (col + row) % ppm; // row can exceed ppm (8 header rows, ppm >= 5)
                 v |= ((cw[src] >> row) & 1u) << col;
             }
             s[row] = (uint16_t)((gray_to_bin(v) << (g.sf - ppm)) & 0xffffu); // :222-225

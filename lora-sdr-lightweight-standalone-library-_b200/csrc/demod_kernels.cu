@@ -15,13 +15,20 @@ static __device__ __forceinline__ float pi_f() { return 3.14159274101257324f; } 
 //   fused caller-dechirp: ((iq * down[i]) * scale) * rot, *= window[i]      performance_test.cpp:109-114 first
 struct Prep {
     const float2* down;   // nullptr = no dechirp
+    int down_ofs;         // table index of in-window sample 0, and the index mask (see below)
+    int down_mask;
     const float* window;  // nullptr = no window multiply
     float scale;          // 1.0f = no normalisation (x * 1.0f is exact)
     bool rotate;
     float rate, start;
     __device__ __forceinline__ float2 operator()(float2 v, int i) const
     {
-        if (down) v = cmul_rn(v, __ldg(down + i));
+        // demodulate() multiplies in-window sample i by down[i] (phy.cpp:221).  The callers of
+        // lora_demodulate() dechirp the whole buffer first, sample n by down[n mod N]
+        // (performance_test.cpp:109-114), and only then does lora_demodulate shift its windows by t_off
+        // (LoRaDemod.cpp:141-151) -- so in fused caller-dechirp mode the table index follows the sample's
+        // ABSOLUTE position: down_ofs = window base mod N.
+        if (down) v = cmul_rn(v, __ldg(down + ((down_ofs + i) & down_mask)));
         v = make_float2(__fmul_rn(v.x, scale), __fmul_rn(v.y, scale));
         if (rotate) {
             const float ph = __fadd_rn(start, __fmul_rn(rate, (float)i));
@@ -118,7 +125,7 @@ estimate_kernel(EstimateArgs a)
     const bool active = t < TPW;
     const float2* x = a.iq + (size_t)p * a.packet_stride;
     float4 e = a.est[p];
-    Prep prep{a.dechirp ? a.down : nullptr, a.window, a.use_scale ? e.z : 1.0f, false, 0.0f, 0.0f};
+    Prep prep{a.dechirp ? a.down : nullptr, 0, N - 1, a.window, a.use_scale ? e.z : 1.0f, false, 0.0f, 0.0f};
 
     float sum_index = 0.0f, phase_diff = 0.0f, prev_phase = 0.0f;
     bool have_prev = false;
@@ -226,7 +233,8 @@ __global__ void __launch_bounds__(DemodShape<SF>::CTA) demod_kernel(DemodArgs a)
             }
             const float start = __fmul_rn(rate, __fadd_rn((float)((size_t)s * N),
                                                           __fdiv_rn((float)t_off, (float)a.osr))); // :213-214
-            const Prep prep{a.dechirp ? a.down : nullptr, a.window, a.use_scale ? e.z : 1.0f, true, rate, start};
+            const int down_ofs = a.dechirp_absolute ? (int)(base & (size_t)(N - 1)) : 0;
+            const Prep prep{a.dechirp ? a.down : nullptr, down_ofs, N - 1, a.window, a.use_scale ? e.z : 1.0f, true, rate, start};
             const float2* x = a.iq + (size_t)p * a.packet_stride + base;
 #pragma unroll 4
             for (int i = t; i < N; i += TPW) F[digit_reverse<SF>(i)] = prep(__ldg(x + (size_t)i * a.osr), i);

@@ -40,6 +40,7 @@ struct DemodArgs {
     int total;           // windows per packet, sync included
     int osr;
     int dechirp, use_scale, have_sync;
+    int dechirp_absolute; // fused caller-dechirp: table index = absolute sample position mod N
     const float2* tw;
     const float2* down;
     const float* window;
