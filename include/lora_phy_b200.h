@@ -105,6 +105,18 @@ unsigned long long lora_b200_launch_count(void);
  * events, returns their summed duration and count since the last call, and resets the counters. */
 int lora_b200_set_kernel_timing(lora_b200_ctx* ctx, int enable);
 int lora_b200_kernel_time(lora_b200_ctx* ctx, double* total_ms, unsigned long long* launches);
+/* How lora_b200_demod_batch resolves windows (SF7..SF12; smaller SF always use the exact kernel).
+ *   FAST  (default) every window goes through the FMA-fused kernel; a window whose two largest |X[k]|^2 are
+ *         closer than the kernel's error bound (relative margin 2^-13, widened with the CFO phase) is recomputed
+ *         by the bit-faithful kernel in a second launch.  Symbol indices are bit-identical to the reference;
+ *         d_peaks is within 1e-4 relative of the reference's float32 value (BASELINE.json's tolerance).
+ *   EXACT every window goes through the bit-faithful kernel: d_peaks is bit-identical as well. */
+#define LORA_B200_PRECISION_FAST 0
+#define LORA_B200_PRECISION_EXACT 1
+int lora_b200_set_precision(lora_b200_ctx* ctx, int precision);
+/* Windows demodulated in FAST precision, and how many of them were rechecked, since the last call
+ * (synchronises the device; for reporting only). */
+int lora_b200_recheck_stats(lora_b200_ctx* ctx, unsigned long long* windows, unsigned long long* rechecked);
 /* Copies of the host-built tables, for tests: table 0 twiddles, 1 down-chirp (n complex), 2 window (n floats). */
 int lora_b200_ctx_table(const lora_b200_ctx* ctx, int table, void* h_out, size_t n);
 

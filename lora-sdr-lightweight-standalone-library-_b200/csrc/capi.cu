@@ -8,7 +8,9 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
+#include <complex>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -16,6 +18,7 @@
 #include <vector>
 
 #include "code_kernels.h"
+#include "demod_fast.h"
 #include "demod_kernels.h"
 #include "host_tables.h"
 #include "mod_kernels.h"
@@ -70,6 +73,12 @@ struct lora_b200_ctx {
     float2* d_tw = nullptr;
     float2* d_down = nullptr;
     float* d_window = nullptr;   // Hann table, or nullptr when window == none
+    float* d_down_turns = nullptr; // phase of d_down in turns (fast demod flavour)
+    Tw0 tw0{};                   // pass-0 twiddles of the register-blocked FFT (kernel arguments)
+    int precision = PRECISION_FAST;
+    Buf flags;                   // recheck list: [0] = count, [1..] = window numbers
+    unsigned long long stat_windows = 0; // windows demodulated in PRECISION_FAST since the last stats call
+    unsigned long long* d_stat_rechecked = nullptr; // device-side running count of rechecked windows
     uint8_t* d_whiten = nullptr; // 2 x WHITEN_LEN bytes
     Buf est, sync_raw;           // per-packet scratch of the demod kernels
     Buf s_iq, s_sym, s_metrics, s_payload, s_results, s_misc; // staging for the host-buffer entry points
@@ -110,6 +119,9 @@ extern "C" int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx**
     c->h_tw = build_twiddles(c->n);
     c->h_down = build_downchirp(c->n, c->bw_scale);
     c->h_window = build_hann(c->n);
+    const std::vector<float> h_turns = build_downchirp_turns(c->n, c->bw_scale);
+    if (blocked_supported(static_cast<int>(cfg->sf)))
+        fill_tw0(static_cast<int>(cfg->sf), reinterpret_cast<const float2*>(c->h_tw.data()), &c->tw0);
     c->h_pin.pinned = true;
     std::vector<uint8_t> wh(2 * WHITEN_LEN);
     build_whitening(wh.data(), wh.data() + WHITEN_LEN, WHITEN_LEN);
@@ -117,11 +129,15 @@ extern "C" int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx**
     const size_t nb = sizeof(float2) * c->n;
     bool ok = cudaMalloc(&c->d_tw, nb) == cudaSuccess && cudaMalloc(&c->d_down, nb) == cudaSuccess &&
               cudaMalloc(&c->d_whiten, wh.size()) == cudaSuccess &&
+              cudaMalloc(&c->d_down_turns, sizeof(float) * c->n) == cudaSuccess &&
+              cudaMalloc(&c->d_stat_rechecked, sizeof(unsigned long long)) == cudaSuccess &&
+              cudaMemset(c->d_stat_rechecked, 0, sizeof(unsigned long long)) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (ok && cfg->window == 1) ok = cudaMalloc(&c->d_window, sizeof(float) * c->n) == cudaSuccess;
     ok = ok && cudaMemcpy(c->d_tw, c->h_tw.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
          cudaMemcpy(c->d_down, c->h_down.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
-         cudaMemcpy(c->d_whiten, wh.data(), wh.size(), cudaMemcpyHostToDevice) == cudaSuccess;
+         cudaMemcpy(c->d_whiten, wh.data(), wh.size(), cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(c->d_down_turns, h_turns.data(), sizeof(float) * c->n, cudaMemcpyHostToDevice) == cudaSuccess;
     if (ok && c->d_window)
         ok = cudaMemcpy(c->d_window, c->h_window.data(), sizeof(float) * c->n, cudaMemcpyHostToDevice) == cudaSuccess;
     if (!ok) {
@@ -137,8 +153,9 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_tw); cudaFree(c->d_down); cudaFree(c->d_window); cudaFree(c->d_whiten);
-    for (Buf* b : {&c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
+    cudaFree(c->d_tw); cudaFree(c->d_down); cudaFree(c->d_window); cudaFree(c->d_whiten); cudaFree(c->d_down_turns);
+    cudaFree(c->d_stat_rechecked);
+    for (Buf* b : {&c->flags, &c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
                    &c->s_misc, &c->h_pin})
         b->release();
     for (auto& pr : c->ev_pool) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -170,6 +187,31 @@ extern "C" int lora_b200_kernel_time(lora_b200_ctx* c, double* total_ms, unsigne
     *total_ms = sum;
     *launches = c->ev_used;
     c->ev_used = 0;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_set_precision(lora_b200_ctx* c, int precision)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (precision != LORA_B200_PRECISION_FAST && precision != LORA_B200_PRECISION_EXACT)
+        return fail(LORA_B200_EINVAL, "unknown precision");
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->precision = precision;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_recheck_stats(lora_b200_ctx* c, unsigned long long* windows, unsigned long long* rechecked)
+{
+    if (!c || !windows || !rechecked) return fail(LORA_B200_EINVAL, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());
+    unsigned long long r = 0;
+    CU(cudaMemcpy(&r, c->d_stat_rechecked, sizeof(r), cudaMemcpyDeviceToHost));
+    CU(cudaMemset(c->d_stat_rechecked, 0, sizeof(r)));
+    *windows = c->stat_windows;
+    *rechecked = r;
+    c->stat_windows = 0;
     return LORA_B200_OK;
 }
 
@@ -212,8 +254,80 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
     CU(c->sync_raw.reserve(sizeof(uint16_t) * 2 * n_packets));
     float4* est = c->est.as<float4>();
     const int np = static_cast<int>(n_packets);
-    CU(launch_fill_est(est, np, st));
     const bool dechirp_in = mode == LORA_B200_DEMOD_LEGACY_DECHIRP;
+
+    if (blocked_supported(static_cast<int>(c->cfg.sf))) {
+        // SF7..SF12: register-blocked kernels (demod_fast.cu).  Batches are cut so that a launch sees < 2^31 windows.
+        const int sf = static_cast<int>(c->cfg.sf);
+        const size_t chunk_packets = total ? std::max<size_t>(1, 0x7fffffffull / total) : n_packets;
+        size_t max_windows = std::min(n_packets, chunk_packets) * total;
+        if (total > 0 && c->precision == PRECISION_FAST) CU(c->flags.reserve(sizeof(unsigned) * (max_windows + 1)));
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        for (size_t p0 = 0; p0 < n_packets; p0 += chunk_packets) {
+            const size_t pn = std::min(chunk_packets, n_packets - p0);
+            PrepassArgs pa{};
+            pa.iq = d_iq + p0 * packet_stride; pa.packet_stride = packet_stride; pa.count = count;
+            pa.n_packets = static_cast<int>(pn);
+            pa.do_maxabs = legacy && count > 0;
+            pa.symbols = static_cast<int>(total < 2 ? total : 2);
+            pa.osr = static_cast<int>(osr);
+            pa.dechirp = dechirp_in;   // demodulate() estimates on RAW samples (phy.cpp:192-193)
+            pa.use_scale = legacy;
+            pa.legacy_tie = legacy;
+            pa.tw = reinterpret_cast<const c64*>(c->d_tw); pa.down = reinterpret_cast<const c64*>(c->d_down);
+            pa.window = c->d_window;
+            pa.power_scale = c->power_scale;
+            pa.est = est + p0;
+            pa.tw0 = c->tw0; pa.one = 1.0f;
+            CU(launch_prepass_blocked(sf, pa, st));
+            if (total == 0) continue;
+
+            BlockedDemodArgs da{};
+            da.iq = pa.iq; da.packet_stride = packet_stride; da.count = count;
+            da.n_windows = static_cast<unsigned>(pn * total);
+            da.total = static_cast<int>(total);
+            da.div_total = make_fastdiv(static_cast<unsigned>(total));
+            da.osr = static_cast<int>(osr);
+            da.dechirp = mode != LORA_B200_DEMOD_LEGACY;
+            da.dechirp_absolute = dechirp_in;
+            da.use_scale = legacy;
+            da.have_sync = have_sync;
+            da.tw = pa.tw; da.down = pa.down; da.down_turns = c->d_down_turns; da.window = c->d_window;
+            da.est = est + p0;
+            da.symbols = d_symbols + p0 * symbol_stride; da.symbol_stride = symbol_stride;
+            da.sync_raw = c->sync_raw.as<uint16_t>() + 2 * p0;
+            da.peaks = d_peaks ? d_peaks + p0 * total : nullptr;
+            da.tw0 = c->tw0; da.one = 1.0f;
+            da.margin = 1.0f / 8192.0f;
+            da.flag_count = c->flags.as<unsigned>();
+            da.flag_list = c->flags.as<unsigned>() ? c->flags.as<unsigned>() + 1 : nullptr;
+            da.flag_cap = da.n_windows;
+            da.stat_rechecked = c->d_stat_rechecked;
+            if (c->timing) {
+                if (c->ev_used == c->ev_pool.size()) {
+                    cudaEvent_t a = nullptr, b = nullptr;
+                    CU(cudaEventCreate(&a));
+                    CU(cudaEventCreate(&b));
+                    c->ev_pool.emplace_back(a, b);
+                }
+                e0 = c->ev_pool[c->ev_used].first;
+                e1 = c->ev_pool[c->ev_used].second;
+                ++c->ev_used;
+                CU(cudaEventRecord(e0, st));
+            }
+            CU(launch_demod_blocked(sf, da, c->precision, c->sm_count, st));
+            if (c->timing) CU(cudaEventRecord(e1, st));
+            if (c->precision == PRECISION_FAST) c->stat_windows += da.n_windows;
+        }
+        if (d_metrics) {
+            FinalizeArgs fa{est, c->sync_raw.as<uint16_t>(), d_metrics, np, static_cast<int>(c->cfg.sf),
+                            have_sync, legacy, static_cast<int>(n_out)};
+            CU(launch_finalize(fa, st));
+        }
+        return LORA_B200_OK;
+    }
+
+    CU(launch_fill_est(est, np, st));
     if (legacy && count > 0) {
         MaxAbsArgs m{d_iq, packet_stride, count, dechirp_in ? c->d_down : nullptr, c->n, est};
         CU(launch_maxabs(m, np, st));
@@ -293,6 +407,22 @@ static int estimate_batch_locked(lora_b200_ctx* c, const float2* d_iq, size_t n_
     CU(c->est.reserve(sizeof(float4) * n_packets));
     CU(c->sync_raw.reserve(sizeof(uint16_t) * 2 * n_packets));
     const int np = static_cast<int>(n_packets);
+    if (blocked_supported(static_cast<int>(c->cfg.sf))) {
+        PrepassArgs pa{};
+        pa.iq = d_iq; pa.packet_stride = packet_stride; pa.count = count;
+        pa.n_packets = np;
+        pa.symbols = static_cast<int>(symbols);
+        pa.osr = static_cast<int>(c->cfg.osr);
+        pa.tw = reinterpret_cast<const c64*>(c->d_tw); pa.down = reinterpret_cast<const c64*>(c->d_down);
+        pa.window = c->d_window;
+        pa.power_scale = c->power_scale;
+        pa.est = c->est.as<float4>();
+        pa.tw0 = c->tw0; pa.one = 1.0f;
+        CU(launch_prepass_blocked(static_cast<int>(c->cfg.sf), pa, st));
+        FinalizeArgs fb{c->est.as<float4>(), c->sync_raw.as<uint16_t>(), d_metrics, np, static_cast<int>(c->cfg.sf), 0, 0, 0};
+        CU(launch_finalize(fb, st));
+        return LORA_B200_OK;
+    }
     CU(launch_fill_est(c->est.as<float4>(), np, st));
     EstimateArgs ea{};
     ea.iq = d_iq; ea.packet_stride = packet_stride;

@@ -1,0 +1,496 @@
+// demod_fast.cu -- the receive hot path for SF7..SF12 on the register-blocked FFT (fft_blocked.cuh).
+//
+//   prepass_kernel   per packet: max-abs normalisation scan (LoRaDemod.cpp:59-77) and the offset estimate over
+//                    the first windows (phy.cpp:78-145 / LoRaDemod.cpp:79-135), bit-faithful.
+//   demod_kernel     per window: dechirp * CFO-rotate * window -> FFT -> |X|^2 argmax (phy.cpp:200-234,
+//                    LoRaDemod.cpp:141-175), in two arithmetic flavours of ONE butterfly graph:
+//                      FAITH  every operation rounded as the reference rounds it, cosf/sinf with glibc's bits;
+//                             symbol index AND peak value are bit-identical to the CPU.
+//                      fast   FMA-fused butterflies, and dechirp+rotation done in the phase domain (one MUFU
+//                             sincos of  down_phase[i] + start + rate*i  per sample).  |X|^2 differs from the
+//                             faithful value by ~1e-6 relative, so the argmax is only trusted when the top two
+//                             bins are separated by more than `margin`; every other window is appended to a
+//                             list and recomputed by the FAITH flavour in a second launch (a floating-point
+//                             filter: the cheap evaluation decides whenever its error bound allows, the exact
+//                             one otherwise).  Symbols are therefore bit-exact in both precisions; peak values
+//                             are exact under PRECISION_EXACT and within 1e-4 relative under PRECISION_FAST.
+#include "demod_fast.h"
+
+#include "demod_kernels.h"
+#include "exact_math.h"
+
+namespace lora_b200 {
+
+namespace {
+
+constexpr float kPiF = 3.14159274101257324f; // float(M_PI)
+constexpr int kCta = 256;
+
+// ---- synchronisation among the threads that share one window -------------------------------------------------
+// TPW threads (a power of two, aligned) own a window: a sub-warp group, a warp, several warps, or the whole CTA.
+template <int TPW>
+struct Group {
+    static PM_DEV unsigned mask()
+    {
+        if (TPW >= 32) return 0xffffffffu;
+        const unsigned lane = threadIdx.x & 31u;
+        return ((1u << (TPW & 31)) - 1u) << (lane & ~(unsigned)(TPW - 1));
+    }
+    static PM_DEV void sync(int slot)
+    {
+        if (TPW <= 32) __syncwarp(mask());
+        else if (TPW == kCta) __syncthreads();
+        else asm volatile("bar.sync %0, %1;" ::"r"(slot + 1), "r"(TPW) : "memory");
+    }
+};
+
+// ---- peak search ---------------------------------------------------------------------------------------------
+// (value, index) ordering of LoRaDetector.hpp:46-58: larger |X|^2 wins, equal values keep the lower index, and
+// a value that is not > 0 (zero, NaN) never wins.  `second` = the largest value that did not win (fast flavour).
+struct Top {
+    float v;
+    int i;
+    float second;
+};
+
+PM_DEV Top top_merge(Top a, Top b)
+{
+    Top r;
+    const bool take_b = b.v > a.v || (b.v == a.v && b.i < a.i);
+    r.v = take_b ? b.v : a.v;
+    r.i = take_b ? b.i : a.i;
+    r.second = fmaxf(fmaxf(a.second, b.second), take_b ? a.v : b.v);
+    return r;
+}
+
+template <int SF, bool FAITH>
+PM_DEV Top thread_top(const c64 (&v)[16], int t)
+{
+    using B = Blk<SF>;
+    constexpr int P = B::NP - 1, Rp = B::R(P), Gp = B::G(P);
+    Top best{0.0f, 0, 0.0f};
+    // ascending bin order for this thread is e-major, g-minor: bin = t + T*(g + G*e); strict '>' keeps the first
+#pragma unroll
+    for (int e = 0; e < Rp; ++e) {
+#pragma unroll
+        for (int g = 0; g < Gp; ++g) {
+            const int i = g * Rp + e;
+            const float m2 = mag2<FAITH>(v[i]);
+            if (!FAITH) best.second = fmaxf(best.second, fminf(best.v, m2));
+            if (m2 > best.v) { best.v = m2; best.i = bin_of<SF>(t, i); }
+        }
+    }
+    return best;
+}
+
+// Reduces over the TPW threads of the window; the result is valid in the window's thread 0 (all threads for TPW<=32).
+template <int TPW>
+PM_DEV Top group_top(Top best, int t, int slot, Top* red)
+{
+    constexpr int W = TPW < 32 ? TPW : 32;
+    const unsigned mask = Group<TPW>::mask();
+#pragma unroll
+    for (int o = W / 2; o > 0; o >>= 1) {
+        Top other;
+        other.v = __shfl_xor_sync(mask, best.v, o);
+        other.i = __shfl_xor_sync(mask, best.i, o);
+        other.second = __shfl_xor_sync(mask, best.second, o);
+        best = top_merge(best, other);
+    }
+    if (TPW > 32) {
+        constexpr int WARPS = TPW / 32;
+        if ((t & 31) == 0) red[slot * WARPS + (t >> 5)] = best;
+        Group<TPW>::sync(slot);
+        if (t == 0) {
+            best = red[slot * WARPS];
+#pragma unroll
+            for (int w = 1; w < WARPS; ++w) best = top_merge(best, red[slot * WARPS + w]);
+        }
+    }
+    return best;
+}
+
+// ---- per-sample preparation -----------------------------------------------------------------------------------
+// Faithful: ((iq * down) * scale) * rot, then * window, each step rounded as phy.cpp:216-225 /
+// LoRaDemod.cpp:73-75,153-160 / tests/performance_test.cpp:109-114 round it.
+struct PrepFaith {
+    const c64* down;     // nullptr = no dechirp
+    int down_ofs, down_mask;
+    const float* window; // nullptr = none
+    float scale;
+    bool rotate;
+    float rate, start, one;
+    PM_DEV c64 operator()(c64 v, int i) const
+    {
+        if (down) v = cmul<true>(v, __ldg(down + ((down_ofs + i) & down_mask)), one);
+        v = cscale(v, scale);
+        if (rotate) {
+            const float ph = __fadd_rn(start, __fmul_rn(rate, (float)i));
+            float sn, cs;
+            xm_sincosf(ph, &sn, &cs); // glibc cosf/sinf bits, exact_math.h
+            v = cmul<true>(v, pk(cs, sn), one);
+        }
+        if (window) v = cscale(v, __ldg(window + i));
+        return v;
+    }
+};
+
+// Fast: iq * exp(2*pi*j*(down_turns[i] + start_t + rate_t*i)), then * window.  The normalisation scale is
+// applied to the peak value instead (|X|^2 is homogeneous of degree 2).
+struct PrepFast {
+    const float* down_turns; // nullptr = no dechirp
+    int down_ofs, down_mask;
+    const float* window;
+    float rate_t, start_t;   // in turns; start_t reduced to [-0.5, 0.5]
+    PM_DEV c64 operator()(c64 v, int i) const
+    {
+        float turns = fmaf(rate_t, (float)i, start_t);
+        if (down_turns) turns += __ldg(down_turns + ((down_ofs + i) & down_mask));
+        float sn, cs;
+        __sincosf(turns * 6.28318530717958648f, &sn, &cs);
+        v = cmul<false>(v, pk(cs, sn), 1.0f);
+        if (window) v = cscale(v, __ldg(window + i));
+        return v;
+    }
+};
+
+
+// What every thread of a window needs to know about it (phy.cpp:197-214, LoRaDemod.cpp:137-151).
+struct WinParams {
+    int p, s;
+    size_t base;
+    float rate, start, scale;
+    int down_ofs;
+};
+
+template <int SF>
+PM_DEV WinParams window_params(const BlockedDemodArgs& a, unsigned w)
+{
+    constexpr int N = 1 << SF;
+    WinParams q;
+    q.p = a.div_total.d == 1 ? (int)w : (int)(__umulhi(w, a.div_total.magic) >> a.div_total.shift);
+    q.s = (int)(w - (unsigned)q.p * (unsigned)a.total);
+    const float4 e = __ldg(a.est + q.p);
+    const size_t step = (size_t)N * a.osr;
+    const int t_off = (int)roundf(e.y);                                                 // phy.cpp:197
+    q.rate = __fdiv_rn(__fmul_rn(-2.0f * kPiF, e.x), (float)N);                          // :198
+    size_t base = (size_t)q.s * step;                                                    // :205-212
+    if (t_off > 0) {
+        if (base + (size_t)t_off + step <= a.count) base += (size_t)t_off;
+    } else if (t_off < 0) {
+        const size_t off = (size_t)(-(long long)t_off);
+        if (off <= base) base -= off;
+    }
+    q.base = base;
+    q.start = __fmul_rn(q.rate, __fadd_rn((float)((size_t)q.s * N), __fdiv_rn((float)t_off, (float)a.osr))); // :213-214
+    q.scale = a.use_scale ? e.z : 1.0f;
+    q.down_ofs = a.dechirp_absolute ? (int)(base & (size_t)(N - 1)) : 0;
+    return q;
+}
+
+// ---- the hot kernel ---------------------------------------------------------------------------------------------
+// A CTA of 256 threads holds 256/T window slots; each slot walks its own sequence of windows, so slots never
+// wait for each other (sub-warp / named-barrier synchronisation only).  LIST = window numbers come from the
+// recheck list instead of 0..n_windows-1.
+template <int SF>
+struct DemodCfg {
+    static constexpr int T = Blk<SF>::T;
+    static constexpr int SLOTS = kCta / T;
+    static constexpr int SMEM_C64 = SLOTS * Blk<SF>::WIN;
+};
+
+template <int SF, bool FAITH, bool LIST>
+__global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T, SLOTS = DemodCfg<SF>::SLOTS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    c64* smem = reinterpret_cast<c64*>(smem_raw);
+    __shared__ Top red[T > 32 ? kCta / 32 : 1];
+    const int slot = threadIdx.x / T;
+    const int t = threadIdx.x % T;
+    c64* S = smem + slot * B::WIN;
+    const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_windows;
+    if (LIST && blockIdx.x == 0 && threadIdx.x == 0 && n_items) atomicAdd(a.stat_rechecked, (unsigned long long)n_items);
+
+    for (unsigned it = blockIdx.x * SLOTS + slot; it < n_items; it += gridDim.x * SLOTS) {
+        const unsigned w = LIST ? a.flag_list[it] : it;
+        const WinParams q = window_params<SF>(a, w);
+        const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)q.p * a.packet_stride + q.base;
+        c64 in[16], v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
+        float peak_scale = 1.0f, margin = 0.0f;
+        if (FAITH) {
+            const PrepFaith prep{a.dechirp ? a.down : nullptr, q.down_ofs, N - 1, a.window, q.scale, true, q.rate, q.start, a.one};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
+        } else {
+            // turns: rate and the window's start phase, reduced in double so that |turns| stays below 2.5
+            const double inv2pi = 0.15915494309189535;
+            double st = (double)q.start * inv2pi;
+            st -= rint(st);
+            const PrepFast prep{a.dechirp ? a.down_turns : nullptr, q.down_ofs, N - 1, a.window,
+                                (float)((double)q.rate * inv2pi), (float)st};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
+            peak_scale = q.scale * q.scale;
+            // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
+            // the trusted margin widens with the magnitude of the phase
+            const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + q.rate * (float)N));
+            margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
+        }
+        fft_blocked<SF, FAITH>(in, v, S, a.tw, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
+        Top best = group_top<T>(thread_top<SF, FAITH>(v, t), t, slot, red);
+        if (t == 0) {
+            bool trusted = true;
+            if (!FAITH) {
+                trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
+                best.v *= peak_scale;
+                if (!trusted) {
+                    const unsigned k = atomicAdd(a.flag_count, 1u);
+                    if (k < a.flag_cap) a.flag_list[k] = w;
+                }
+            }
+            if (!a.have_sync) a.symbols[(size_t)q.p * a.symbol_stride + q.s] = (uint16_t)best.i;
+            else if (q.s >= 2) a.symbols[(size_t)q.p * a.symbol_stride + (q.s - 2)] = (uint16_t)best.i;
+            else a.sync_raw[2 * (size_t)q.p + q.s] = (uint16_t)best.i;
+            if (a.peaks) a.peaks[w] = best.v;
+        }
+        Group<T>::sync(slot); // the window's exchange region (and red[]) is reused by the next iteration
+    }
+}
+
+
+// ---- prepass: normalisation scan + offset estimate, one packet per group of TPK threads --------------------------
+template <int SF>
+struct PreCfg {
+    static constexpr int T = Blk<SF>::T;
+    static constexpr int TPK = T > 32 ? T : 32;  // threads per packet
+    static constexpr int SLOTS = kCta / TPK;
+    static constexpr int SMEM_C64 = SLOTS * Blk<SF>::WIN;
+};
+
+template <int SF>
+__global__ void __launch_bounds__(kCta) prepass_blocked_kernel(const __grid_constant__ PrepassArgs a)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T, TPK = PreCfg<SF>::TPK, SLOTS = PreCfg<SF>::SLOTS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    c64* smem = reinterpret_cast<c64*>(smem_raw);
+    __shared__ Top red[kCta / 32];
+    __shared__ float redf[kCta / 32];
+    const int slot = threadIdx.x / TPK;
+    const int u = threadIdx.x % TPK;
+    c64* S = smem + slot * B::WIN;
+    const int p = blockIdx.x * SLOTS + slot;
+    if (p >= a.n_packets) return; // whole slots leave together; slots never synchronise with each other
+    const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride;
+    float4 e = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+
+    // LoRaDemod.cpp:59-77: max over all samples of max(|re|,|im|), comparisons written so a NaN never wins.
+    // In fused-dechirp mode the values examined are iq * down[n mod N] (performance_test.cpp:109-114).
+    if (a.do_maxabs) {
+        float mx = 0.0f;
+        for (size_t n = u; n < a.count; n += TPK) {
+            c64 v = __ldg(x + n);
+            if (a.dechirp) v = cmul<true>(v, __ldg(a.down + (n & (size_t)(N - 1))), a.one);
+            const float2 f = up(v);
+            const float r = fabsf(f.x), im = fabsf(f.y);
+            const float m = (r < im) ? im : r;
+            if (m > mx) mx = m;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const float y = __shfl_xor_sync(0xffffffffu, mx, o); if (y > mx) mx = y; }
+        if (TPK > 32) {
+            if ((u & 31) == 0) redf[slot * (TPK / 32) + (u >> 5)] = mx;
+            Group<TPK>::sync(slot);
+            mx = redf[slot * (TPK / 32)];
+#pragma unroll
+            for (int w = 1; w < TPK / 32; ++w) if (redf[slot * (TPK / 32) + w] > mx) mx = redf[slot * (TPK / 32) + w];
+        }
+        e.w = mx;
+        e.z = (mx > 1.0f) ? __fdiv_rn(1.0f, mx) : 1.0f;
+    }
+
+    // phy.cpp:78-145 and its twin LoRaDemod.cpp:79-135
+    float sum_index = 0.0f, phase_diff = 0.0f, prev_phase = 0.0f;
+    bool have_prev = false;
+    unsigned sum_t = 0;
+    const size_t step = (size_t)N * a.osr;
+    const PrepFaith prep{a.dechirp ? a.down : nullptr, 0, N - 1, a.window, a.use_scale ? e.z : 1.0f, false, 0.0f, 0.0f, a.one};
+    for (int s = 0; s < a.symbols; ++s) {
+        float best_p = -1e30f, best_f = 0.0f;
+        int best_idx = 0;
+        unsigned best_t = 0;
+        float2 best_bin = make_float2(0.0f, 0.0f);
+        for (unsigned ph = 0; ph < (unsigned)a.osr; ++ph) {
+            Top pk_{0.0f, 0, 0.0f};
+            if (u < T) {
+                c64 in[16], v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) in[j] = prep(__ldg(x + s * step + ph + (size_t)(u + T * j) * a.osr), u + T * j);
+                fft_blocked<SF, true>(in, v, S, a.tw, a.tw0, u, a.one, [slot] { Group<T>::sync(slot); });
+                pk_ = thread_top<SF, true>(v, u);
+                Group<T>::sync(slot); // all exchange loads done: the region now receives the natural-order spectrum
+#pragma unroll
+                for (int i = 0; i < 16; ++i) S[bin_of<SF>(u, i)] = v[i];
+            }
+            Group<TPK>::sync(slot);
+            pk_ = group_top<TPK>(pk_, u, slot, red);
+            if (u == 0) { // LoRaDetector.hpp:60-71
+                const float fundamental = __fsqrt_rn(pk_.v);
+                const float pw = __fsub_rn(__fmul_rn(20.0f, log10f(fundamental)), a.power_scale);
+                const float2 Lb = up(S[pk_.i > 0 ? pk_.i - 1 : N - 1]);
+                const float2 Rb = up(S[pk_.i < N - 1 ? pk_.i + 1 : 0]);
+                const float left = xm_hypotf(Lb.x, Lb.y), right = xm_hypotf(Rb.x, Rb.y);
+                const double demon = __dsub_rn(__dsub_rn(__dmul_rn(2.0, (double)fundamental), (double)right), (double)left);
+                const float fi = (demon == 0.0) ? 0.0f : (float)__ddiv_rn(__dmul_rn(0.5, (double)__fsub_rn(right, left)), demon);
+                if (pw > best_p || (a.legacy_tie && pw == best_p && pk_.i < best_idx)) {
+                    best_p = pw; best_idx = pk_.i; best_f = fi; best_t = ph; best_bin = up(S[pk_.i]);
+                }
+            }
+            Group<TPK>::sync(slot);
+        }
+        if (u == 0) {
+            sum_t += best_t;
+            sum_index = __fadd_rn(sum_index, __fadd_rn((float)best_idx, best_f));
+            const float phase = xm_atan2f(best_bin.y, best_bin.x); // std::arg
+            if (have_prev) {
+                float d = __fsub_rn(phase, prev_phase);
+                const float two_pi = __fmul_rn(2.0f, kPiF);
+                while (d > kPiF) d = __fsub_rn(d, two_pi);
+                while (d < -kPiF) d = __fadd_rn(d, two_pi);
+                phase_diff = __fadd_rn(phase_diff, d);
+            }
+            prev_phase = phase;
+            have_prev = true;
+        }
+    }
+    if (u == 0) {
+        if (a.symbols > 0) {
+            const float Sn = (float)a.symbols;
+            const float avg_index = __fdiv_rn(sum_index, Sn);
+            const float cfo_coarse = __fdiv_rn(avg_index, (float)N);
+            float cfo_fine = 0.0f;
+            if (a.symbols > 1)
+                cfo_fine = __fdiv_rn(__fdiv_rn(phase_diff, (float)(a.symbols - 1)), __fmul_rn(__fmul_rn(2.0f, kPiF), (float)N));
+            e.x = __fadd_rn(cfo_coarse, cfo_fine);
+            const float frac = __fsub_rn(avg_index, floorf(__fadd_rn(avg_index, 0.5f)));
+            const float avg_t = __fdiv_rn((float)sum_t, Sn);
+            e.y = __fsub_rn(avg_t, __fmul_rn(__fmul_rn(frac, (float)N), (float)a.osr));
+        }
+        a.est[p] = e;
+    }
+}
+
+} // namespace
+
+// ---- launchers ---------------------------------------------------------------------------------------------------
+FastDiv make_fastdiv(unsigned d)
+{
+    FastDiv f{d, 0u, 0u};
+    if (d <= 1) return f;
+    unsigned lg = 0;
+    while ((1ull << lg) < d) ++lg;                    // ceil(log2 d)
+    const unsigned k = 31 + lg;
+    f.magic = (unsigned)(((1ull << k) + d - 1) / d);   // ceil(2^k / d) < 2^32
+    f.shift = k - 32;
+    return f;
+}
+
+bool blocked_supported(int sf) { return sf >= 7 && sf <= 12; }
+
+template <int SF>
+static void fill_tw0_sf(const float2* h_tw, Tw0* out)
+{
+    using B = Blk<SF>;
+    const int Fa = B::F(B::pa(0));
+    for (int k = 0; k < 4; ++k)
+        for (int q = 0; q < 4; ++q) out->w[k * 4 + q] = h_tw[(k * Fa * q) & (B::N - 1)];
+}
+
+void fill_tw0(int sf, const float2* h_tw, Tw0* out)
+{
+    switch (sf) {
+    case 7: fill_tw0_sf<7>(h_tw, out); break;
+    case 8: fill_tw0_sf<8>(h_tw, out); break;
+    case 9: fill_tw0_sf<9>(h_tw, out); break;
+    case 10: fill_tw0_sf<10>(h_tw, out); break;
+    case 11: fill_tw0_sf<11>(h_tw, out); break;
+    case 12: fill_tw0_sf<12>(h_tw, out); break;
+    default: break;
+    }
+}
+
+template <int SF>
+static cudaError_t launch_prepass_sf(const PrepassArgs& a, cudaStream_t st)
+{
+    constexpr int SLOTS = PreCfg<SF>::SLOTS;
+    constexpr size_t smem = sizeof(c64) * PreCfg<SF>::SMEM_C64;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(prepass_blocked_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    const int grid = (a.n_packets + SLOTS - 1) / SLOTS;
+    prepass_blocked_kernel<SF><<<grid, kCta, smem, st>>>(a);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
+template <int SF, bool FAITH, bool LIST>
+static cudaError_t launch_demod_one(const BlockedDemodArgs& a, int sm_count, unsigned items_hint, cudaStream_t st)
+{
+    constexpr int SLOTS = DemodCfg<SF>::SLOTS;
+    constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64;
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        cudaError_t e = cudaFuncSetAttribute(demod_blocked_kernel<SF, FAITH, LIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, demod_blocked_kernel<SF, FAITH, LIST>, kCta, smem);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) per_sm = 1;
+    }
+    long long grid = (long long)sm_count * per_sm; // whole waves of resident CTAs; slots stride over the windows
+    const long long need = ((long long)items_hint + SLOTS - 1) / SLOTS;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    demod_blocked_kernel<SF, FAITH, LIST><<<(unsigned)grid, kCta, smem, st>>>(a);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
+template <int SF>
+static cudaError_t launch_demod_sf(const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
+{
+    if (precision == PRECISION_EXACT) return launch_demod_one<SF, true, false>(a, sm_count, a.n_windows, st);
+    cudaError_t e = cudaMemsetAsync(a.flag_count, 0, sizeof(unsigned), st);
+    if (e != cudaSuccess) return e;
+    e = launch_demod_one<SF, false, false>(a, sm_count, a.n_windows, st);
+    if (e != cudaSuccess) return e;
+    // the recheck list is short (about 1e-3 of the windows on noise); a quarter-wave grid is plenty, and its
+    // size must not depend on a device-side count
+    return launch_demod_one<SF, true, true>(a, sm_count, (unsigned)(sm_count * DemodCfg<SF>::SLOTS), st);
+}
+
+#define LORA_BLOCKED_SWITCH(fn, ...)          \
+    switch (sf) {                             \
+    case 7: return fn<7>(__VA_ARGS__);        \
+    case 8: return fn<8>(__VA_ARGS__);        \
+    case 9: return fn<9>(__VA_ARGS__);        \
+    case 10: return fn<10>(__VA_ARGS__);      \
+    case 11: return fn<11>(__VA_ARGS__);      \
+    case 12: return fn<12>(__VA_ARGS__);      \
+    default: return cudaErrorInvalidValue;    \
+    }
+
+cudaError_t launch_prepass_blocked(int sf, const PrepassArgs& a, cudaStream_t st) { LORA_BLOCKED_SWITCH(launch_prepass_sf, a, st) }
+
+cudaError_t launch_demod_blocked(int sf, const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
+{
+    LORA_BLOCKED_SWITCH(launch_demod_sf, a, precision, sm_count, st)
+}
+
+} // namespace lora_b200

@@ -1,0 +1,223 @@
+// fft_blocked.cuh -- the reference's 2^SF-point FFT as a register-blocked schedule of the SAME butterfly graph.
+//
+// kissfft for N = 2^SF is a decimation-in-time recursion with radix list 4,4,...[,2] (kissfft.hh:80-97): stage s
+// (0 = outermost) has remainder m_s = N/(r_0..r_s) and twiddle stride F_s = r_0..r_{s-1}; its butterflies
+// (kf_bfly4 :164-185, kf_bfly2 :155-162) combine positions base + q*m_s with twiddles tw[k*F_s*q],
+// k = position mod m_s.  A butterfly is a pure function of its operands, so any schedule of the same graph
+// gives the same bits.  The schedule here:
+//
+//   * a window is owned by T = N/16 threads, 16 points each, held in registers as packed (re,im) pairs;
+//   * the stages are grouped, innermost first, into passes of two stages (radix 16 = 4*4, or 8 = 2*4 for the
+//     innermost pass of an odd SF, or a lone radix-4 outermost stage): SF7 8.16, SF8 16.16, SF9 8.16.4,
+//     SF10 16.16.4, SF11 8.16.16, SF12 16.16.16;
+//   * pass 0 needs, per thread, exactly the input samples t + T*j (j = 0..15): the mixed-radix digit reversal
+//     of kissfft's leaf copy (:114-120) becomes a compile-time register permutation, and the global loads are
+//     coalesced;
+//   * between passes the points are exchanged through shared memory at pad(position); pad() is chosen per SF
+//     so that every 64-bit exchange access is bank-conflict free (searched by scripts/fft_schedule_model.py),
+//     and pad(base + e*m) = pad(base) + pad(e*m), so every access is one LDS/STS with an immediate offset;
+//   * after the last pass thread t holds bins t + T*(g + G*e) in natural order, and the |X|^2 argmax runs on
+//     registers -- the spectrum is never written anywhere.
+//
+// FAITH = true keeps every multiplication the reference performs (including the ones by tw[0] = 1+0j) as
+// separately rounded IEEE operations: bit-identical to the CPU.  FAITH = false fuses multiply-adds and skips
+// the multiplications by 1.
+#pragma once
+
+#include "packed_math.cuh"
+
+namespace lora_b200 {
+
+template <int SF>
+struct Blk {
+    static constexpr int N = 1 << SF;
+    static constexpr int L4 = SF / 2;        // radix-4 stages
+    static constexpr int L = (SF + 1) / 2;   // stages in all
+    static constexpr int T = N / 16;         // threads per window
+    static constexpr int NP = (L + 1) / 2;   // passes
+    __host__ __device__ static constexpr int radix(int s) { return s < L4 ? 4 : 2; }
+    __host__ __device__ static constexpr int m(int s) { int p = 1; for (int u = 0; u <= s; ++u) p *= radix(u); return N / p; }
+    __host__ __device__ static constexpr int F(int s) { int p = 1; for (int u = 0; u < s; ++u) p *= radix(u); return p; }
+    // pass p (0 = innermost, executed first) covers stages pa(p)..pb(p)
+    __host__ __device__ static constexpr int pb(int p) { return L - 1 - 2 * p; }
+    __host__ __device__ static constexpr int pa(int p) { return pb(p) >= 1 ? pb(p) - 1 : 0; }
+    __host__ __device__ static constexpr int R(int p) { int r = 1; for (int s = pa(p); s <= pb(p); ++s) r *= radix(s); return r; }
+    __host__ __device__ static constexpr int G(int p) { return 16 / R(p); }
+    __host__ __device__ static constexpr int pad(int X)
+    {
+        return SF == 7 ? X + (X >> 3) + (X >> 4) : SF == 8 ? X + (X >> 4) : X + (X >> 4) + (X >> 8);
+    }
+    // shared-memory footprint of one window, in c64 units; chosen = 8 (mod 16) for SF7 so that the four
+    // windows of a warp interleave over all banks
+    static constexpr int WIN = SF == 7 ? 152 : SF == 8 ? 272 : ((pad(N - 1) + 1 + 1) & ~1);
+    // digit of element e (position order inside the pass) at stage s
+    __host__ __device__ static constexpr int digit(int p, int s, int e) { return (e / (m(s) / m(pb(p)))) % radix(s); }
+    // pass 0: register slot of the j-th loaded sample (input index t + T*j)
+    __host__ __device__ static constexpr int slot0(int j)
+    {
+        const int g = j % G(0), jj = j / G(0);
+        int e = 0, rem = jj;
+        for (int s = pa(0); s <= pb(0); ++s) { e += (rem % radix(s)) * (m(s) / m(pb(0))); rem /= radix(s); }
+        return g * R(0) + e;
+    }
+};
+
+// The 16 twiddles pass 0 can need, tw0[k*4+q] = tw[k * F(pa(0)) * q]; thread-independent, so they travel as
+// kernel arguments (constant bank) instead of being loaded.
+struct Tw0 {
+    float2 w[16];
+};
+
+template <int SF, bool FAITH, bool GUARD>
+PM_DEV void bfly4(c64& f0, c64& f1, c64& f2, c64& f3, c64 w1, c64 w2, c64 w3, bool trivial, float one)
+{
+    c64 s0 = f1, s1 = f2, s2 = f3;
+    if (FAITH || !trivial) { s0 = cmul<FAITH>(f1, w1, one); s1 = cmul<FAITH>(f2, w2, one); s2 = cmul<FAITH>(f3, w3, one); }
+    const c64 s5 = GUARD ? csub_g<FAITH>(f0, s1, one) : sub2(f0, s1);
+    const c64 g0 = GUARD ? cadd_g<FAITH>(f0, s1, one) : add2(f0, s1);
+    const c64 s3 = add2(s0, s2);
+    const c64 s4 = mul_mj(sub2(s0, s2));
+    f2 = sub2(g0, s3);
+    f0 = add2(g0, s3);
+    f1 = add2(s5, s4);
+    f3 = sub2(s5, s4);
+}
+
+template <int SF, bool FAITH, bool GUARD>
+PM_DEV void bfly2(c64& f0, c64& f1, c64 w1, bool trivial, float one)
+{
+    c64 x = f1;
+    if (FAITH || !trivial) x = cmul<FAITH>(f1, w1, one);
+    f1 = GUARD ? csub_g<FAITH>(f0, x, one) : sub2(f0, x);
+    f0 = GUARD ? cadd_g<FAITH>(f0, x, one) : add2(f0, x);
+}
+
+// All stages of pass P on the 16 register-resident points of one thread.  klowF[g] = (position mod m_b) of
+// group g (0 in pass 0).
+template <int SF, int P, bool FAITH>
+PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restrict__ tw, const Tw0& tw0, float one)
+{
+    using B = Blk<SF>;
+    constexpr int a = B::pa(P), b = B::pb(P), Rp = B::R(P), Gp = B::G(P), mb = B::m(b);
+#pragma unroll
+    for (int s = b; s >= a; --s) {
+        const int w = B::m(s) / mb;      // register stride of this stage's digit
+        const int rs = B::radix(s);
+        const int Fs = B::F(s);
+#pragma unroll
+        for (int g = 0; g < Gp; ++g) {
+#pragma unroll
+            for (int e0 = 0; e0 < Rp; ++e0) {
+                if (B::digit(P, s, e0) != 0) continue;
+                int cpart = 0; // contribution of the in-pass digits below stage s to k
+#pragma unroll
+                for (int u = s + 1; u <= b; ++u) cpart += B::digit(P, u, e0) * B::m(u);
+                const int i0 = g * Rp + e0;
+                c64 w1, w2 = 0, w3 = 0;
+                bool trivial;
+                if (P == 0) { // k = cpart, thread independent
+                    trivial = cpart == 0;
+                    const int k = cpart; // < radix(b) <= 4, and only the outer stage of the pass has k != 0
+                    w1 = pk(tw0.w[k * 4 + 1].x, tw0.w[k * 4 + 1].y);
+                    if (rs == 4) {
+                        w2 = pk(tw0.w[k * 4 + 2].x, tw0.w[k * 4 + 2].y);
+                        w3 = pk(tw0.w[k * 4 + 3].x, tw0.w[k * 4 + 3].y);
+                    }
+                } else {
+                    trivial = false;
+                    const int kF = (cpart + klow[g]) * Fs;
+                    w1 = __ldg(tw + kF);
+                    if (rs == 4) { w2 = __ldg(tw + 2 * kF); w3 = __ldg(tw + 3 * kF); }
+                }
+                constexpr bool dummy = false; (void)dummy;
+                if (rs == 4) {
+                    if (P == 0 && s == b) bfly4<SF, FAITH, true>(v[i0], v[i0 + w], v[i0 + 2 * w], v[i0 + 3 * w], w1, w2, w3, trivial, one);
+                    else bfly4<SF, FAITH, false>(v[i0], v[i0 + w], v[i0 + 2 * w], v[i0 + 3 * w], w1, w2, w3, trivial, one);
+                } else {
+                    if (P == 0 && s == b) bfly2<SF, FAITH, true>(v[i0], v[i0 + w], w1, trivial, one);
+                    else bfly2<SF, FAITH, false>(v[i0], v[i0 + w], w1, trivial, one);
+                }
+            }
+        }
+    }
+}
+
+// Position base of group g of thread t in pass P, and the klow it implies.
+template <int SF, int P>
+PM_DEV int group_base(int t, int g, int& klow)
+{
+    using B = Blk<SF>;
+    constexpr int a = B::pa(P), mb = B::m(B::pb(P)), Rp = B::R(P);
+    const int gam = t + B::T * g;
+    if (P == 0) { // digit reversal of the input base index over the stages outside the pass (all radix 4)
+        int X = 0, rem = gam;
+#pragma unroll
+        for (int s = 0; s < a; ++s) { X += (rem & 3) * B::m(s); rem >>= 2; }
+        klow = 0;
+        return X;
+    }
+    klow = gam & (mb - 1);
+    return (gam / mb) * (Rp * mb) + klow;
+}
+
+template <int SF, int P>
+PM_DEV void exchange_store(const c64 (&v)[16], c64* __restrict__ S, int t)
+{
+    using B = Blk<SF>;
+    constexpr int Rp = B::R(P), Gp = B::G(P), mb = B::m(B::pb(P));
+#pragma unroll
+    for (int g = 0; g < Gp; ++g) {
+        int kl;
+        const int A = B::pad(group_base<SF, P>(t, g, kl));
+#pragma unroll
+        for (int e = 0; e < Rp; ++e) S[A + B::pad(e * mb)] = v[g * Rp + e];
+    }
+}
+
+template <int SF, int P>
+PM_DEV void exchange_load(c64 (&v)[16], int (&klow)[4], const c64* __restrict__ S, int t)
+{
+    using B = Blk<SF>;
+    constexpr int Rp = B::R(P), Gp = B::G(P), mb = B::m(B::pb(P));
+#pragma unroll
+    for (int g = 0; g < Gp; ++g) {
+        const int A = B::pad(group_base<SF, P>(t, g, klow[g]));
+#pragma unroll
+        for (int e = 0; e < Rp; ++e) v[g * Rp + e] = S[A + B::pad(e * mb)];
+    }
+}
+
+// Whole transform.  `in[j]` = preprocessed input sample t + T*j; on return `v[i]` holds bin bin_of<SF>(t, i).
+// S = this window's shared-memory region (Blk<SF>::WIN entries); sync() = barrier over the window's T threads.
+template <int SF, bool FAITH, typename Sync>
+PM_DEV void fft_blocked(const c64 (&in)[16], c64 (&v)[16], c64* __restrict__ S, const c64* __restrict__ tw,
+                        const Tw0& tw0, int t, float one, Sync sync)
+{
+    using B = Blk<SF>;
+    int klow[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[B::slot0(j)] = in[j];
+    pass_stages<SF, 0, FAITH>(v, klow, tw, tw0, one);
+    exchange_store<SF, 0>(v, S, t);
+    sync();
+    exchange_load<SF, 1>(v, klow, S, t);
+    pass_stages<SF, 1, FAITH>(v, klow, tw, tw0, one);
+    if (B::NP == 3) {
+        sync(); // every pass-1 load is done before the in-place stores
+        exchange_store<SF, 1>(v, S, t);
+        sync();
+        exchange_load<SF, (B::NP == 3 ? 2 : 1)>(v, klow, S, t);
+        pass_stages<SF, (B::NP == 3 ? 2 : 1), FAITH>(v, klow, tw, tw0, one);
+    }
+}
+
+// Natural-order bin held in register i of thread t after fft_blocked.
+template <int SF>
+__host__ __device__ constexpr int bin_of(int t, int i)
+{
+    using B = Blk<SF>;
+    constexpr int P = B::NP - 1;
+    return t + B::T * (i / B::R(P)) + (i % B::R(P)) * B::m(B::pb(P));
+}
+
+} // namespace lora_b200

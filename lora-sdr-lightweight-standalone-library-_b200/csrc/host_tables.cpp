@@ -43,6 +43,27 @@ std::vector<std::complex<float>> build_downchirp(int n, float bw_scale)
     return d;
 }
 
+std::vector<float> build_downchirp_turns(int n, float bw_scale)
+{
+    // the same recurrence as host_gen_chirp(n, 1, n, 0, down, 1, phase = 0), keeping the float32 phase itself
+    const double pi = 3.14159265358979323846;
+    const float lo = static_cast<float>(-pi * bw_scale);
+    const float hi = static_cast<float>(pi * bw_scale);
+    const float inc = static_cast<float>((2 * pi * bw_scale) / n);
+    const float span = hi - lo;
+    float f = lo + 0.0f;
+    float acc = 0.0f;
+    std::vector<float> turns(static_cast<size_t>(n));
+    for (int i = 0; i < n; ++i) {
+        f += inc;
+        if (f > hi) f -= span;
+        acc = acc - f;
+        const double t = static_cast<double>(acc) / (2 * pi);
+        turns[i] = static_cast<float>(t - std::nearbyint(t));
+    }
+    return turns;
+}
+
 std::vector<float> build_hann(int n)
 {
     std::vector<float> w(static_cast<size_t>(n));

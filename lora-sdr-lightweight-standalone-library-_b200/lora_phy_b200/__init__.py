@@ -17,6 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "liblora_phy_b200.so")
 
 DEMOD_WORKSPACE, DEMOD_LEGACY, DEMOD_LEGACY_DECHIRP = 0, 1, 2
+PRECISION_FAST, PRECISION_EXACT = 0, 1
 PAYLOAD_STRIDE = 264
 
 
@@ -59,6 +60,8 @@ _SIGNATURES = {
     "lora_b200_launch_count": (C.c_ulonglong, []),
     "lora_b200_set_kernel_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "lora_b200_kernel_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]),
+    "lora_b200_set_precision": (C.c_int, [C.c_void_p, C.c_int]),
+    "lora_b200_recheck_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
     "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -141,6 +144,17 @@ class Context:
             self.h = None
 
     __del__ = close
+
+    def set_precision(self, precision):
+        """PRECISION_FAST (default): fused kernel + bit-faithful recheck of near-tie windows; PRECISION_EXACT:
+        bit-faithful kernel on every window (peak values bit-identical too)."""
+        _check(self.lib.lora_b200_set_precision(self.h, int(precision)))
+
+    def recheck_stats(self):
+        """-> (windows demodulated in FAST precision, windows rechecked) since the last call."""
+        w, r = C.c_ulonglong(), C.c_ulonglong()
+        _check(self.lib.lora_b200_recheck_stats(self.h, C.byref(w), C.byref(r)))
+        return w.value, r.value
 
     def set_kernel_timing(self, enable):
         _check(self.lib.lora_b200_set_kernel_timing(self.h, int(enable)))

@@ -111,9 +111,11 @@ def test_batch_vs_oracle_seeded(env, sf, bw, osr, window):
     clean = ctx.modulate_batch(d_tx).cpu().numpy()
     for p in (0, n_pk - 1):
         assert bits(clean[p]) == bits(ORC.lora_modulate(tx[p], sf, osr, bw))
-    for mode in (L.DEMOD_WORKSPACE, L.DEMOD_LEGACY, L.DEMOD_LEGACY_DECHIRP):
+    for mode, precision in [(m, pr) for m in (L.DEMOD_WORKSPACE, L.DEMOD_LEGACY, L.DEMOD_LEGACY_DECHIRP)
+                            for pr in (L.PRECISION_EXACT, L.PRECISION_FAST)]:
         if mode == L.DEMOD_LEGACY_DECHIRP and osr != 1:
             continue
+        ctx.set_precision(precision)
         sym, met, peaks = ctx.demod_batch(iq, mode=mode, want_peaks=True)
         sym = sym.cpu().numpy().view(np.uint16)
         met = met.cpu().numpy().view(L.PKT_METRICS).reshape(-1)
@@ -131,7 +133,10 @@ def test_batch_vs_oracle_seeded(env, sf, bw, osr, window):
             assert int(met[p]["sync_word"]) == sync_o
             assert bits(met[p]["cfo"]) == bits(np.float32(mo.cfo)), (sf, mode, p)
             assert bits(met[p]["time_offset"]) == bits(np.float32(mo.time_offset))
-            assert bits(peaks[p]) == bits(pk), (sf, mode, p)  # bound would be 1e-4 relative on sqrt(peak)
+            if precision == L.PRECISION_EXACT or sf < 7:
+                assert bits(peaks[p]) == bits(pk), (sf, mode, p)
+            else:  # BASELINE.json: FFT peak magnitudes within 1e-4 relative in fp32 (|X|, so 2e-4 on |X|^2)
+                np.testing.assert_allclose(np.sqrt(peaks[p]), np.sqrt(pk), rtol=1e-4, atol=0)
 
 
 def test_legacy_edge_cases(env):
@@ -248,3 +253,30 @@ def test_full_size_round_trip_property(env, sf):
     assert torch.equal(rx, sym)
     rx2, _, _ = ctx.demod_batch(iq, mode=L.DEMOD_LEGACY_DECHIRP)
     assert int(rx.to(torch.int64).sum()) == int(rx2.to(torch.int64).sum())
+
+
+@pytest.mark.parametrize("sf", range(7, 13))
+def test_fast_precision_filter(env, sf):
+    """PRECISION_FAST = fused kernel + bit-faithful recheck of near-tie windows.  On mostly-noise input (where
+    near ties are common) the symbols must equal PRECISION_EXACT's on every window, the peaks must agree far
+    inside the 1e-4 budget, and the recheck rate must be the small fraction the margin predicts."""
+    L, torch = env["L"], env["torch"]
+    ctx = L.Context(sf)
+    n_pk, nsym = (2048 >> max(0, sf - 9)), 14
+    gen = torch.Generator(device="cuda").manual_seed(100 + sf)
+    tx = torch.randint(0, 1 << sf, (n_pk, nsym), dtype=torch.int16, device="cuda", generator=gen)
+    iq = ctx.modulate_batch(tx)
+    snr = torch.tensor([-30.0, -20.0, -12.0, 0.0], device="cuda")[torch.arange(n_pk, device="cuda") % 4]
+    ctx.awgn_batch(iq, snr.contiguous(), seed=sf)
+    for mode in (L.DEMOD_LEGACY_DECHIRP, L.DEMOD_WORKSPACE):
+        ctx.set_precision(L.PRECISION_EXACT)
+        s0, m0, p0 = ctx.demod_batch(iq, mode=mode, want_peaks=True)
+        ctx.set_precision(L.PRECISION_FAST)
+        ctx.recheck_stats()
+        s1, m1, p1 = ctx.demod_batch(iq, mode=mode, want_peaks=True)
+        windows, rechecked = ctx.recheck_stats()
+        assert torch.equal(s0, s1), (sf, mode, int((s0 != s1).sum()))
+        assert torch.equal(m0, m1)
+        rel = ((p1 - p0).abs() / p0).max().item()
+        assert rel < 2e-5, (sf, mode, rel)
+        assert windows == n_pk * (nsym + 2) and 0 < rechecked < 0.02 * windows, (sf, mode, windows, rechecked)
