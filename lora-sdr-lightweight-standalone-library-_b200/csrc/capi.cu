@@ -73,7 +73,8 @@ struct lora_b200_ctx {
     float2* d_tw = nullptr;
     float2* d_down = nullptr;
     float* d_window = nullptr;   // Hann table, or nullptr when window == none
-    float* d_down_turns = nullptr; // phase of d_down in turns (fast demod flavour)
+    float* d_down_phase = nullptr; // phase of d_down in radians, 2N entries (fast demod flavour)
+    float2* d_twp = nullptr;       // per-stage twiddle table of the register-blocked FFT
     Tw0 tw0{};                   // pass-0 twiddles of the register-blocked FFT (kernel arguments)
     int precision = PRECISION_FAST;
     Buf flags;                   // recheck list: [0] = count, [1..] = window numbers
@@ -119,25 +120,35 @@ extern "C" int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx**
     c->h_tw = build_twiddles(c->n);
     c->h_down = build_downchirp(c->n, c->bw_scale);
     c->h_window = build_hann(c->n);
-    const std::vector<float> h_turns = build_downchirp_turns(c->n, c->bw_scale);
+    std::vector<float> h_phase = build_downchirp_phase(c->n, c->bw_scale);
+    h_phase.resize(2 * static_cast<size_t>(c->n)); // stored twice: no index wrap in the kernels
+    std::copy(h_phase.begin(), h_phase.begin() + c->n, h_phase.begin() + c->n);
+    std::vector<float2> h_twp;
     if (blocked_supported(static_cast<int>(cfg->sf)))
+    {
         fill_tw0(static_cast<int>(cfg->sf), reinterpret_cast<const float2*>(c->h_tw.data()), &c->tw0);
+        h_twp = build_stage_twiddles(static_cast<int>(cfg->sf), reinterpret_cast<const float2*>(c->h_tw.data()));
+    }
+    if (h_twp.empty()) h_twp.assign(1, make_float2(1.0f, 0.0f));
     c->h_pin.pinned = true;
     std::vector<uint8_t> wh(2 * WHITEN_LEN);
     build_whitening(wh.data(), wh.data() + WHITEN_LEN, WHITEN_LEN);
 
     const size_t nb = sizeof(float2) * c->n;
-    bool ok = cudaMalloc(&c->d_tw, nb) == cudaSuccess && cudaMalloc(&c->d_down, nb) == cudaSuccess &&
+    bool ok = cudaMalloc(&c->d_tw, nb) == cudaSuccess && cudaMalloc(&c->d_down, 2 * nb) == cudaSuccess &&
+              cudaMalloc(&c->d_twp, sizeof(float2) * h_twp.size()) == cudaSuccess &&
               cudaMalloc(&c->d_whiten, wh.size()) == cudaSuccess &&
-              cudaMalloc(&c->d_down_turns, sizeof(float) * c->n) == cudaSuccess &&
+              cudaMalloc(&c->d_down_phase, sizeof(float) * 2 * c->n) == cudaSuccess &&
               cudaMalloc(&c->d_stat_rechecked, sizeof(unsigned long long)) == cudaSuccess &&
               cudaMemset(c->d_stat_rechecked, 0, sizeof(unsigned long long)) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (ok && cfg->window == 1) ok = cudaMalloc(&c->d_window, sizeof(float) * c->n) == cudaSuccess;
     ok = ok && cudaMemcpy(c->d_tw, c->h_tw.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
          cudaMemcpy(c->d_down, c->h_down.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(c->d_down + c->n, c->h_down.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
+         cudaMemcpy(c->d_twp, h_twp.data(), sizeof(float2) * h_twp.size(), cudaMemcpyHostToDevice) == cudaSuccess &&
          cudaMemcpy(c->d_whiten, wh.data(), wh.size(), cudaMemcpyHostToDevice) == cudaSuccess &&
-         cudaMemcpy(c->d_down_turns, h_turns.data(), sizeof(float) * c->n, cudaMemcpyHostToDevice) == cudaSuccess;
+         cudaMemcpy(c->d_down_phase, h_phase.data(), sizeof(float) * 2 * c->n, cudaMemcpyHostToDevice) == cudaSuccess;
     if (ok && c->d_window)
         ok = cudaMemcpy(c->d_window, c->h_window.data(), sizeof(float) * c->n, cudaMemcpyHostToDevice) == cudaSuccess;
     if (!ok) {
@@ -153,7 +164,7 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_tw); cudaFree(c->d_down); cudaFree(c->d_window); cudaFree(c->d_whiten); cudaFree(c->d_down_turns);
+    cudaFree(c->d_tw); cudaFree(c->d_down); cudaFree(c->d_window); cudaFree(c->d_whiten); cudaFree(c->d_down_phase); cudaFree(c->d_twp);
     cudaFree(c->d_stat_rechecked);
     for (Buf* b : {&c->flags, &c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
                    &c->s_misc, &c->h_pin})
@@ -274,7 +285,7 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             pa.dechirp = dechirp_in;   // demodulate() estimates on RAW samples (phy.cpp:192-193)
             pa.use_scale = legacy;
             pa.legacy_tie = legacy;
-            pa.tw = reinterpret_cast<const c64*>(c->d_tw); pa.down = reinterpret_cast<const c64*>(c->d_down);
+            pa.twp = reinterpret_cast<const c64*>(c->d_twp); pa.down = reinterpret_cast<const c64*>(c->d_down);
             pa.window = c->d_window;
             pa.power_scale = c->power_scale;
             pa.est = est + p0;
@@ -292,7 +303,7 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             da.dechirp_absolute = dechirp_in;
             da.use_scale = legacy;
             da.have_sync = have_sync;
-            da.tw = pa.tw; da.down = pa.down; da.down_turns = c->d_down_turns; da.window = c->d_window;
+            da.twp = pa.twp; da.down = pa.down; da.down_phase = c->d_down_phase; da.window = c->d_window;
             da.est = est + p0;
             da.symbols = d_symbols + p0 * symbol_stride; da.symbol_stride = symbol_stride;
             da.sync_raw = c->sync_raw.as<uint16_t>() + 2 * p0;
@@ -413,7 +424,7 @@ static int estimate_batch_locked(lora_b200_ctx* c, const float2* d_iq, size_t n_
         pa.n_packets = np;
         pa.symbols = static_cast<int>(symbols);
         pa.osr = static_cast<int>(c->cfg.osr);
-        pa.tw = reinterpret_cast<const c64*>(c->d_tw); pa.down = reinterpret_cast<const c64*>(c->d_down);
+        pa.twp = reinterpret_cast<const c64*>(c->d_twp); pa.down = reinterpret_cast<const c64*>(c->d_down);
         pa.window = c->d_window;
         pa.power_scale = c->power_scale;
         pa.est = c->est.as<float4>();

@@ -112,17 +112,17 @@ PM_DEV Top group_top(Top best, int t, int slot, Top* red)
 
 // ---- per-sample preparation -----------------------------------------------------------------------------------
 // Faithful: ((iq * down) * scale) * rot, then * window, each step rounded as phy.cpp:216-225 /
-// LoRaDemod.cpp:73-75,153-160 / tests/performance_test.cpp:109-114 round it.
+// LoRaDemod.cpp:73-75,153-160 / tests/performance_test.cpp:109-114 round it.  `down` points at the entry of
+// the DOUBLED table (2N entries, so no index wrap) that multiplies in-window sample 0.
 struct PrepFaith {
     const c64* down;     // nullptr = no dechirp
-    int down_ofs, down_mask;
     const float* window; // nullptr = none
     float scale;
     bool rotate;
     float rate, start, one;
     PM_DEV c64 operator()(c64 v, int i) const
     {
-        if (down) v = cmul<true>(v, __ldg(down + ((down_ofs + i) & down_mask)), one);
+        if (down) v = cmul<true>(v, __ldg(down + i), one);
         v = cscale(v, scale);
         if (rotate) {
             const float ph = __fadd_rn(start, __fmul_rn(rate, (float)i));
@@ -135,63 +135,77 @@ struct PrepFaith {
     }
 };
 
-// Fast: iq * exp(2*pi*j*(down_turns[i] + start_t + rate_t*i)), then * window.  The normalisation scale is
-// applied to the peak value instead (|X|^2 is homogeneous of degree 2).
+// Fast: iq * exp(j*(down_phase[i] + start + rate*i)), then * window: dechirp and CFO rotation as ONE phase and
+// one MUFU sin/cos pair.  `base` = start (reduced to [-pi, pi]) + rate*t for this thread; sample j of the thread
+// is at in-window index t + T*j, so its phase is base + rate*(T*j) + down_phase[t + T*j].  The normalisation
+// scale is applied to the peak value instead (|X|^2 is homogeneous of degree 2).
 struct PrepFast {
-    const float* down_turns; // nullptr = no dechirp
-    int down_ofs, down_mask;
-    const float* window;
-    float rate_t, start_t;   // in turns; start_t reduced to [-0.5, 0.5]
-    PM_DEV c64 operator()(c64 v, int i) const
+    const float* down_phase; // nullptr = no dechirp; else doubled table + down_ofs + t
+    const float* window;     // nullptr or window + t
+    float rate, base;
+    template <int OFS> PM_DEV c64 apply(c64 v) const
     {
-        float turns = fmaf(rate_t, (float)i, start_t);
-        if (down_turns) turns += __ldg(down_turns + ((down_ofs + i) & down_mask));
+        float ph = fmaf(rate, (float)OFS, base);
+        if (down_phase) ph += __ldg(down_phase + OFS);
         float sn, cs;
-        __sincosf(turns * 6.28318530717958648f, &sn, &cs);
+        __sincosf(ph, &sn, &cs);
         v = cmul<false>(v, pk(cs, sn), 1.0f);
-        if (window) v = cscale(v, __ldg(window + i));
+        if (window) v = cscale(v, __ldg(window + OFS));
         return v;
     }
 };
 
+// What every thread of a window needs to know about its packet and window (phy.cpp:197-214, LoRaDemod.cpp:137-151).
+struct PktParams {
+    int t_off;
+    float rate, scale;
+};
 
-// What every thread of a window needs to know about it (phy.cpp:197-214, LoRaDemod.cpp:137-151).
+template <int SF>
+PM_DEV PktParams packet_params(const BlockedDemodArgs& a, int p)
+{
+    constexpr int N = 1 << SF;
+    const float4 e = __ldg(a.est + p);
+    PktParams k;
+    k.t_off = (int)roundf(e.y);                                                  // phy.cpp:197
+    // :198  -2*pi*cfo / N; N is a power of two, so the division is the exact scaling by 1/N
+    k.rate = __fmul_rn(__fmul_rn(-2.0f * kPiF, e.x), 1.0f / (float)N);
+    k.scale = a.use_scale ? e.z : 1.0f;
+    return k;
+}
+
 struct WinParams {
-    int p, s;
     size_t base;
-    float rate, start, scale;
+    float start;
     int down_ofs;
 };
 
 template <int SF>
-PM_DEV WinParams window_params(const BlockedDemodArgs& a, unsigned w)
+PM_DEV WinParams window_params(const BlockedDemodArgs& a, const PktParams& k, int s)
 {
     constexpr int N = 1 << SF;
     WinParams q;
-    q.p = a.div_total.d == 1 ? (int)w : (int)(__umulhi(w, a.div_total.magic) >> a.div_total.shift);
-    q.s = (int)(w - (unsigned)q.p * (unsigned)a.total);
-    const float4 e = __ldg(a.est + q.p);
     const size_t step = (size_t)N * a.osr;
-    const int t_off = (int)roundf(e.y);                                                 // phy.cpp:197
-    q.rate = __fdiv_rn(__fmul_rn(-2.0f * kPiF, e.x), (float)N);                          // :198
-    size_t base = (size_t)q.s * step;                                                    // :205-212
-    if (t_off > 0) {
-        if (base + (size_t)t_off + step <= a.count) base += (size_t)t_off;
-    } else if (t_off < 0) {
-        const size_t off = (size_t)(-(long long)t_off);
+    size_t base = (size_t)s * step;                                              // phy.cpp:205-212
+    if (k.t_off > 0) {
+        if (base + (size_t)k.t_off + step <= a.count) base += (size_t)k.t_off;
+    } else if (k.t_off < 0) {
+        const size_t off = (size_t)(-(long long)k.t_off);
         if (off <= base) base -= off;
     }
     q.base = base;
-    q.start = __fmul_rn(q.rate, __fadd_rn((float)((size_t)q.s * N), __fdiv_rn((float)t_off, (float)a.osr))); // :213-214
-    q.scale = a.use_scale ? e.z : 1.0f;
+    const float toff_f = a.osr == 1 ? (float)k.t_off : __fdiv_rn((float)k.t_off, (float)a.osr);
+    q.start = __fmul_rn(k.rate, __fadd_rn((float)((size_t)s * N), toff_f));      // :213-214
     q.down_ofs = a.dechirp_absolute ? (int)(base & (size_t)(N - 1)) : 0;
     return q;
 }
 
 // ---- the hot kernel ---------------------------------------------------------------------------------------------
-// A CTA of 256 threads holds 256/T window slots; each slot walks its own sequence of windows, so slots never
+// A CTA of 256 threads holds 256/T window slots; each slot walks its own sequence of window chunks (a chunk =
+// `chunk` consecutive windows, normally of one packet, so the per-packet values are loaded once), and slots never
 // wait for each other (sub-warp / named-barrier synchronisation only).  LIST = window numbers come from the
-// recheck list instead of 0..n_windows-1.
+// recheck list instead of 0..n_windows-1.  OSR1 = oversampling ratio is 1 (every BASELINE config): sample
+// addresses become one pointer per window plus immediate offsets.
 template <int SF>
 struct DemodCfg {
     static constexpr int T = Blk<SF>::T;
@@ -199,7 +213,7 @@ struct DemodCfg {
     static constexpr int SMEM_C64 = SLOTS * Blk<SF>::WIN;
 };
 
-template <int SF, bool FAITH, bool LIST>
+template <int SF, bool FAITH, bool LIST, bool OSR1>
 __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
 {
     using B = Blk<SF>;
@@ -212,55 +226,78 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
     c64* S = smem + slot * B::WIN;
     const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_windows;
     if (LIST && blockIdx.x == 0 && threadIdx.x == 0 && n_items) atomicAdd(a.stat_rechecked, (unsigned long long)n_items);
+    const unsigned chunk = LIST ? 1u : a.chunk;
+    const unsigned n_chunks = (n_items + chunk - 1) / chunk;
 
-    for (unsigned it = blockIdx.x * SLOTS + slot; it < n_items; it += gridDim.x * SLOTS) {
-        const unsigned w = LIST ? a.flag_list[it] : it;
-        const WinParams q = window_params<SF>(a, w);
-        const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)q.p * a.packet_stride + q.base;
-        c64 in[16], v[16];
+    for (unsigned c = blockIdx.x * SLOTS + slot; c < n_chunks; c += gridDim.x * SLOTS) {
+        unsigned w = c * chunk;
+        const unsigned w_end = min(w + chunk, n_items);
+        unsigned wn = LIST ? a.flag_list[w] : w;
+        int p = a.div_total.d == 1 ? (int)wn : (int)(__umulhi(wn, a.div_total.magic) >> a.div_total.shift);
+        int s = (int)(wn - (unsigned)p * (unsigned)a.total);
+        PktParams pk_ = packet_params<SF>(a, p);
+        for (; w < w_end; ++w) {
+            const WinParams q = window_params<SF>(a, pk_, s);
+            const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
+            c64 in[16], v[16];
+            if (OSR1) {
+                const c64* xt = x + t;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
-        float peak_scale = 1.0f, margin = 0.0f;
-        if (FAITH) {
-            const PrepFaith prep{a.dechirp ? a.down : nullptr, q.down_ofs, N - 1, a.window, q.scale, true, q.rate, q.start, a.one};
+                for (int j = 0; j < 16; ++j) in[j] = __ldg(xt + T * j);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
-        } else {
-            // turns: rate and the window's start phase, reduced in double so that |turns| stays below 2.5
-            const double inv2pi = 0.15915494309189535;
-            double st = (double)q.start * inv2pi;
-            st -= rint(st);
-            const PrepFast prep{a.dechirp ? a.down_turns : nullptr, q.down_ofs, N - 1, a.window,
-                                (float)((double)q.rate * inv2pi), (float)st};
-#pragma unroll
-            for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
-            peak_scale = q.scale * q.scale;
-            // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
-            // the trusted margin widens with the magnitude of the phase
-            const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + q.rate * (float)N));
-            margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
-        }
-        fft_blocked<SF, FAITH>(in, v, S, a.tw, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
-        Top best = group_top<T>(thread_top<SF, FAITH>(v, t), t, slot, red);
-        if (t == 0) {
-            bool trusted = true;
-            if (!FAITH) {
-                trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
-                best.v *= peak_scale;
-                if (!trusted) {
-                    const unsigned k = atomicAdd(a.flag_count, 1u);
-                    if (k < a.flag_cap) a.flag_list[k] = w;
-                }
+                for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
             }
-            if (!a.have_sync) a.symbols[(size_t)q.p * a.symbol_stride + q.s] = (uint16_t)best.i;
-            else if (q.s >= 2) a.symbols[(size_t)q.p * a.symbol_stride + (q.s - 2)] = (uint16_t)best.i;
-            else a.sync_raw[2 * (size_t)q.p + q.s] = (uint16_t)best.i;
-            if (a.peaks) a.peaks[w] = best.v;
+            float peak_scale = 1.0f, margin = 0.0f;
+            if (FAITH) {
+                const PrepFaith prep{a.dechirp ? a.down + q.down_ofs : nullptr, a.window, pk_.scale, true, pk_.rate, q.start, a.one};
+#pragma unroll
+                for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
+            } else {
+                // start reduced to [-pi, pi] (Cody-Waite, two constants), so every phase stays below ~16 rad
+                const float kk = rintf(q.start * 0.15915494309189535f);
+                float st = fmaf(-kk, 6.28318548202514648f, q.start);
+                st = fmaf(-kk, -1.74845553146951715e-7f, st);
+                const PrepFast prep{a.dechirp ? a.down_phase + q.down_ofs + t : nullptr, a.window ? a.window + t : nullptr,
+                                    pk_.rate, fmaf(pk_.rate, (float)t, st)};
+                in[0] = prep.template apply<0 * T>(in[0]);   in[1] = prep.template apply<1 * T>(in[1]);
+                in[2] = prep.template apply<2 * T>(in[2]);   in[3] = prep.template apply<3 * T>(in[3]);
+                in[4] = prep.template apply<4 * T>(in[4]);   in[5] = prep.template apply<5 * T>(in[5]);
+                in[6] = prep.template apply<6 * T>(in[6]);   in[7] = prep.template apply<7 * T>(in[7]);
+                in[8] = prep.template apply<8 * T>(in[8]);   in[9] = prep.template apply<9 * T>(in[9]);
+                in[10] = prep.template apply<10 * T>(in[10]); in[11] = prep.template apply<11 * T>(in[11]);
+                in[12] = prep.template apply<12 * T>(in[12]); in[13] = prep.template apply<13 * T>(in[13]);
+                in[14] = prep.template apply<14 * T>(in[14]); in[15] = prep.template apply<15 * T>(in[15]);
+                peak_scale = pk_.scale * pk_.scale;
+                // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
+                // the trusted margin widens with the magnitude of the phase
+                const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
+                margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
+            }
+            fft_blocked<SF, FAITH>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
+            Top best = group_top<T>(thread_top<SF, FAITH>(v, t), t, slot, red);
+            if (t == 0) {
+                if (!FAITH) {
+                    const bool trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
+                    best.v *= peak_scale;
+                    if (!trusted) {
+                        const unsigned k = atomicAdd(a.flag_count, 1u);
+                        if (k < a.flag_cap) a.flag_list[k] = wn;
+                    }
+                }
+                if (!a.have_sync) a.symbols[(size_t)p * a.symbol_stride + s] = (uint16_t)best.i;
+                else if (s >= 2) a.symbols[(size_t)p * a.symbol_stride + (s - 2)] = (uint16_t)best.i;
+                else a.sync_raw[2 * (size_t)p + s] = (uint16_t)best.i;
+                if (a.peaks) a.peaks[wn] = best.v;
+            }
+            Group<T>::sync(slot); // the window's exchange region (and red[]) is reused by the next iteration
+            if (!LIST) { // next window of the chunk
+                ++wn;
+                if (++s == a.total) { s = 0; ++p; if (w + 1 < w_end) pk_ = packet_params<SF>(a, p); }
+            }
         }
-        Group<T>::sync(slot); // the window's exchange region (and red[]) is reused by the next iteration
     }
 }
-
 
 // ---- prepass: normalisation scan + offset estimate, one packet per group of TPK threads --------------------------
 template <int SF>
@@ -318,7 +355,7 @@ __global__ void __launch_bounds__(kCta) prepass_blocked_kernel(const __grid_cons
     bool have_prev = false;
     unsigned sum_t = 0;
     const size_t step = (size_t)N * a.osr;
-    const PrepFaith prep{a.dechirp ? a.down : nullptr, 0, N - 1, a.window, a.use_scale ? e.z : 1.0f, false, 0.0f, 0.0f, a.one};
+    const PrepFaith prep{a.dechirp ? a.down : nullptr, a.window, a.use_scale ? e.z : 1.0f, false, 0.0f, 0.0f, a.one};
     for (int s = 0; s < a.symbols; ++s) {
         float best_p = -1e30f, best_f = 0.0f;
         int best_idx = 0;
@@ -330,7 +367,7 @@ __global__ void __launch_bounds__(kCta) prepass_blocked_kernel(const __grid_cons
                 c64 in[16], v[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) in[j] = prep(__ldg(x + s * step + ph + (size_t)(u + T * j) * a.osr), u + T * j);
-                fft_blocked<SF, true>(in, v, S, a.tw, a.tw0, u, a.one, [slot] { Group<T>::sync(slot); });
+                fft_blocked<SF, true>(in, v, S, a.twp, a.tw0, u, a.one, [slot] { Group<T>::sync(slot); });
                 pk_ = thread_top<SF, true>(v, u);
                 Group<T>::sync(slot); // all exchange loads done: the region now receives the natural-order spectrum
 #pragma unroll
@@ -410,6 +447,31 @@ static void fill_tw0_sf(const float2* h_tw, Tw0* out)
         for (int q = 0; q < 4; ++q) out->w[k * 4 + q] = h_tw[(k * Fa * q) & (B::N - 1)];
 }
 
+template <int SF>
+static void stage_twiddles_sf(const float2* h_tw, std::vector<float2>& out)
+{
+    using B = Blk<SF>;
+    out.assign(B::TWP, make_float2(1.0f, 0.0f));
+    for (int s = 0; s < B::L; ++s)
+        for (int q = 1; q < B::radix(s); ++q)
+            for (int k = 0; k < B::m(s); ++k) out[B::toff(s) + (q - 1) * B::m(s) + k] = h_tw[k * B::F(s) * q];
+}
+
+std::vector<float2> build_stage_twiddles(int sf, const float2* h_tw)
+{
+    std::vector<float2> out;
+    switch (sf) {
+    case 7: stage_twiddles_sf<7>(h_tw, out); break;
+    case 8: stage_twiddles_sf<8>(h_tw, out); break;
+    case 9: stage_twiddles_sf<9>(h_tw, out); break;
+    case 10: stage_twiddles_sf<10>(h_tw, out); break;
+    case 11: stage_twiddles_sf<11>(h_tw, out); break;
+    case 12: stage_twiddles_sf<12>(h_tw, out); break;
+    default: break;
+    }
+    return out;
+}
+
 void fill_tw0(int sf, const float2* h_tw, Tw0* out)
 {
     switch (sf) {
@@ -440,39 +502,50 @@ static cudaError_t launch_prepass_sf(const PrepassArgs& a, cudaStream_t st)
     return cudaGetLastError();
 }
 
-template <int SF, bool FAITH, bool LIST>
-static cudaError_t launch_demod_one(const BlockedDemodArgs& a, int sm_count, unsigned items_hint, cudaStream_t st)
+template <int SF, bool FAITH, bool LIST, bool OSR1>
+static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, unsigned items_hint, cudaStream_t st)
 {
     constexpr int SLOTS = DemodCfg<SF>::SLOTS;
     constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64;
     static int per_sm = 0;
     if (per_sm == 0) {
-        cudaError_t e = cudaFuncSetAttribute(demod_blocked_kernel<SF, FAITH, LIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(demod_blocked_kernel<SF, FAITH, LIST, OSR1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, demod_blocked_kernel<SF, FAITH, LIST>, kCta, smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, demod_blocked_kernel<SF, FAITH, LIST, OSR1>, kCta, smem);
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
     }
-    long long grid = (long long)sm_count * per_sm; // whole waves of resident CTAs; slots stride over the windows
-    const long long need = ((long long)items_hint + SLOTS - 1) / SLOTS;
+    long long grid = (long long)sm_count * per_sm; // whole waves of resident CTAs; slots stride over the window chunks
+    // chunk: consecutive windows one slot takes at a time; at least ~8 chunks per slot for balance
+    const long long slots = grid * SLOTS;
+    long long chunk = (long long)items_hint / (slots * 8);
+    a.chunk = (unsigned)(chunk < 1 ? 1 : chunk > 16 ? 16 : chunk);
+    const long long need = ((long long)items_hint + (long long)SLOTS * a.chunk - 1) / ((long long)SLOTS * a.chunk);
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
-    demod_blocked_kernel<SF, FAITH, LIST><<<(unsigned)grid, kCta, smem, st>>>(a);
+    demod_blocked_kernel<SF, FAITH, LIST, OSR1><<<(unsigned)grid, kCta, smem, st>>>(a);
     ++g_launches;
     return cudaGetLastError();
+}
+
+template <int SF, bool OSR1>
+static cudaError_t launch_demod_osr(const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
+{
+    if (precision == PRECISION_EXACT) return launch_demod_one<SF, true, false, OSR1>(a, sm_count, a.n_windows, st);
+    cudaError_t e = cudaMemsetAsync(a.flag_count, 0, sizeof(unsigned), st);
+    if (e != cudaSuccess) return e;
+    e = launch_demod_one<SF, false, false, OSR1>(a, sm_count, a.n_windows, st);
+    if (e != cudaSuccess) return e;
+    // the recheck list is short (about 1e-3 of the windows on noise); one CTA per SM is plenty, and the grid
+    // size must not depend on a device-side count
+    return launch_demod_one<SF, true, true, OSR1>(a, sm_count, (unsigned)(sm_count * DemodCfg<SF>::SLOTS), st);
 }
 
 template <int SF>
 static cudaError_t launch_demod_sf(const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
 {
-    if (precision == PRECISION_EXACT) return launch_demod_one<SF, true, false>(a, sm_count, a.n_windows, st);
-    cudaError_t e = cudaMemsetAsync(a.flag_count, 0, sizeof(unsigned), st);
-    if (e != cudaSuccess) return e;
-    e = launch_demod_one<SF, false, false>(a, sm_count, a.n_windows, st);
-    if (e != cudaSuccess) return e;
-    // the recheck list is short (about 1e-3 of the windows on noise); a quarter-wave grid is plenty, and its
-    // size must not depend on a device-side count
-    return launch_demod_one<SF, true, true>(a, sm_count, (unsigned)(sm_count * DemodCfg<SF>::SLOTS), st);
+    return a.osr == 1 ? launch_demod_osr<SF, true>(a, precision, sm_count, st)
+                      : launch_demod_osr<SF, false>(a, precision, sm_count, st);
 }
 
 #define LORA_BLOCKED_SWITCH(fn, ...)          \

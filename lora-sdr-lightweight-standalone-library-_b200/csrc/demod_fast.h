@@ -5,6 +5,8 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#include <vector>
+
 #include "fft_blocked.cuh"
 
 namespace lora_b200 {
@@ -30,9 +32,10 @@ struct BlockedDemodArgs {
     int osr;
     int dechirp, use_scale, have_sync;
     int dechirp_absolute;   // fused caller-dechirp: table index = absolute sample position mod N
-    const c64* tw;          // N twiddles, exp(-2*pi*j*i/N) as kissfft.hh:24-29 builds them
-    const c64* down;        // N-entry reference down-chirp table (ChirpGenerator.hpp:24-50)
-    const float* down_turns; // phase of down[i] in turns, in [-0.5, 0.5)
+    const c64* twp;         // per-stage twiddle table (Blk::toff): the values of kissfft.hh:24-29, regrouped
+    const c64* down;        // reference down-chirp table (ChirpGenerator.hpp:24-50), stored twice back to back
+    const float* down_phase; // phase of down[i] in radians in [-pi, pi], stored twice back to back
+    unsigned chunk;         // consecutive windows a slot takes at a time (set by the launcher)
     const float* window;    // Hann table or nullptr
     const float4* est;      // per packet: x = cfo, y = time_offset, z = scale, w = max_amp
     uint16_t* symbols;
@@ -58,8 +61,8 @@ struct PrepassArgs {
     int dechirp;       // multiply by the down-chirp first (fused caller-dechirp only)
     int use_scale;     // apply est[p].z
     int legacy_tie;    // LoRaDemod.cpp:101 lowest-index rule on equal power
-    const c64* tw;
-    const c64* down;
+    const c64* twp;    // per-stage twiddle table
+    const c64* down;   // doubled down-chirp table
     const float* window;
     float power_scale; // float(20*log10(N)), LoRaDetector.hpp:29
     float4* est;
@@ -72,6 +75,8 @@ cudaError_t launch_prepass_blocked(int sf, const PrepassArgs& a, cudaStream_t st
 cudaError_t launch_demod_blocked(int sf, const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st);
 // Fills the pass-0 twiddle block from the host twiddle table.
 void fill_tw0(int sf, const float2* h_tw, Tw0* out);
+// The per-stage regrouping of the twiddle table the blocked kernels read (Blk::TWP entries).
+std::vector<float2> build_stage_twiddles(int sf, const float2* h_tw);
 bool blocked_supported(int sf);
 
 } // namespace lora_b200

@@ -50,6 +50,11 @@ struct Blk {
     // shared-memory footprint of one window, in c64 units; chosen = 8 (mod 16) for SF7 so that the four
     // windows of a warp interleave over all banks
     static constexpr int WIN = SF == 7 ? 152 : SF == 8 ? 272 : ((pad(N - 1) + 1 + 1) & ~1);
+    // Per-stage twiddle table: stage s, multiplier q (1..radix-1), k in [0, m_s) lives at toff(s) + (q-1)*m_s + k
+    // and holds tw[k*F_s*q] -- the same values kissfft indexes, laid out so that the threads of a window (consecutive
+    // k) read consecutive entries.
+    __host__ __device__ static constexpr int toff(int s) { int o = 0; for (int u = 0; u < s; ++u) o += (radix(u) - 1) * m(u); return o; }
+    static constexpr int TWP = N + 16; // entries allocated (the table needs N-1, or N for odd SF)
     // digit of element e (position order inside the pass) at stage s
     __host__ __device__ static constexpr int digit(int p, int s, int e) { return (e / (m(s) / m(pb(p)))) % radix(s); }
     // pass 0: register slot of the j-th loaded sample (input index t + T*j)
@@ -92,8 +97,8 @@ PM_DEV void bfly2(c64& f0, c64& f1, c64 w1, bool trivial, float one)
     f0 = GUARD ? cadd_g<FAITH>(f0, x, one) : add2(f0, x);
 }
 
-// All stages of pass P on the 16 register-resident points of one thread.  klowF[g] = (position mod m_b) of
-// group g (0 in pass 0).
+// All stages of pass P on the 16 register-resident points of one thread.  klow[g] = (position mod m_b) of
+// group g (0 in pass 0).  `tw` is the per-stage table (Blk::toff).
 template <int SF, int P, bool FAITH>
 PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restrict__ tw, const Tw0& tw0, float one)
 {
@@ -103,7 +108,6 @@ PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restric
     for (int s = b; s >= a; --s) {
         const int w = B::m(s) / mb;      // register stride of this stage's digit
         const int rs = B::radix(s);
-        const int Fs = B::F(s);
 #pragma unroll
         for (int g = 0; g < Gp; ++g) {
 #pragma unroll
@@ -125,9 +129,9 @@ PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restric
                     }
                 } else {
                     trivial = false;
-                    const int kF = (cpart + klow[g]) * Fs;
-                    w1 = __ldg(tw + kF);
-                    if (rs == 4) { w2 = __ldg(tw + 2 * kF); w3 = __ldg(tw + 3 * kF); }
+                    const c64* wp = tw + klow[g] + (B::toff(s) + cpart); // per-stage table, immediate offsets
+                    w1 = __ldg(wp);
+                    if (rs == 4) { w2 = __ldg(wp + B::m(s)); w3 = __ldg(wp + 2 * B::m(s)); }
                 }
                 constexpr bool dummy = false; (void)dummy;
                 if (rs == 4) {
@@ -188,7 +192,8 @@ PM_DEV void exchange_load(c64 (&v)[16], int (&klow)[4], const c64* __restrict__ 
 }
 
 // Whole transform.  `in[j]` = preprocessed input sample t + T*j; on return `v[i]` holds bin bin_of<SF>(t, i).
-// S = this window's shared-memory region (Blk<SF>::WIN entries); sync() = barrier over the window's T threads.
+// S = this window's shared-memory region (Blk<SF>::WIN entries); sync() = barrier over the window's T threads;
+// tw = the per-stage twiddle table.  The caller must sync() before S is written again (next window).
 template <int SF, bool FAITH, typename Sync>
 PM_DEV void fft_blocked(const c64 (&in)[16], c64 (&v)[16], c64* __restrict__ S, const c64* __restrict__ tw,
                         const Tw0& tw0, int t, float one, Sync sync)
@@ -203,8 +208,8 @@ PM_DEV void fft_blocked(const c64 (&in)[16], c64 (&v)[16], c64* __restrict__ S, 
     exchange_load<SF, 1>(v, klow, S, t);
     pass_stages<SF, 1, FAITH>(v, klow, tw, tw0, one);
     if (B::NP == 3) {
-        sync(); // every pass-1 load is done before the in-place stores
-        exchange_store<SF, 1>(v, S, t);
+        exchange_store<SF, 1>(v, S, t); // in place: a thread overwrites exactly the positions it read
+
         sync();
         exchange_load<SF, (B::NP == 3 ? 2 : 1)>(v, klow, S, t);
         pass_stages<SF, (B::NP == 3 ? 2 : 1), FAITH>(v, klow, tw, tw0, one);

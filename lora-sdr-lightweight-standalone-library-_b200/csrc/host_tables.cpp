@@ -43,7 +43,7 @@ std::vector<std::complex<float>> build_downchirp(int n, float bw_scale)
     return d;
 }
 
-std::vector<float> build_downchirp_turns(int n, float bw_scale)
+std::vector<float> build_downchirp_phase(int n, float bw_scale)
 {
     // the same recurrence as host_gen_chirp(n, 1, n, 0, down, 1, phase = 0), keeping the float32 phase itself
     const double pi = 3.14159265358979323846;
@@ -59,7 +59,7 @@ std::vector<float> build_downchirp_turns(int n, float bw_scale)
         if (f > hi) f -= span;
         acc = acc - f;
         const double t = static_cast<double>(acc) / (2 * pi);
-        turns[i] = static_cast<float>(t - std::nearbyint(t));
+        turns[i] = static_cast<float>((t - std::nearbyint(t)) * (2 * pi));
     }
     return turns;
 }

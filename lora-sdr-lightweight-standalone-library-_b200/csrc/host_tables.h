@@ -13,10 +13,10 @@ std::vector<std::complex<float>> build_twiddles(int n);
 // The table demodulate() regenerates every symbol: genChirp(N, 1, N, 0, down, 1, phase=0, bw_scale)
 // (src/phy/phy.cpp:202-204 -> include/lora_phy/ChirpGenerator.hpp:24-50).
 std::vector<std::complex<float>> build_downchirp(int n, float bw_scale);
-// Phase of every entry of that table, in turns reduced to [-0.5, 0.5]: the float32 accumulator the recurrence
-// holds when it emits the entry, divided by 2*pi in double.  Used by the fast demod flavour, which applies
-// dechirp and CFO rotation as one phase.
-std::vector<float> build_downchirp_turns(int n, float bw_scale);
+// Phase of every entry of that table in radians, reduced to [-pi, pi] in double: the float32 accumulator the
+// recurrence holds when it emits the entry.  Used by the fast demod flavour, which applies dechirp and CFO
+// rotation as one phase.
+std::vector<float> build_downchirp_phase(int n, float bw_scale);
 // 0.5 - 0.5*cos(2*pi*i/(N-1)) in float (src/phy/phy.cpp:36-43).
 std::vector<float> build_hann(int n);
 // float(20*log10(N)), include/lora_phy/LoRaDetector.hpp:29.
