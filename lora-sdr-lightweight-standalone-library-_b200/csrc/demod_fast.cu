@@ -110,6 +110,69 @@ PM_DEV Top group_top(Top best, int t, int slot, Top* red)
     return best;
 }
 
+// Peak of one window for the demod kernels.  For TPW >= 32 the warp-level part uses three REDUX operations on
+// the value bits (|X|^2 >= 0, so unsigned order = float order) instead of a 5-round (value, index, second)
+// shuffle butterfly, and the bin index is only searched by the thread(s) that hold the maximum.
+template <int SF, bool FAITH, int TPW>
+PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red)
+{
+    if (TPW < 32) return group_top<TPW>(thread_top<SF, FAITH>(v, t), t, slot, red);
+    using B = Blk<SF>;
+    constexpr int P = B::NP - 1, Rp = B::R(P), Gp = B::G(P);
+    float m2[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) m2[i] = mag2<FAITH>(v[i]);
+    // largest (and, fast flavour, second largest counting duplicates) of the thread's 16 values; NaN is ignored
+    float hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { hi[i] = fmaxf(m2[2 * i], m2[2 * i + 1]); lo[i] = fminf(m2[2 * i], m2[2 * i + 1]); }
+#pragma unroll
+    for (int n = 4; n >= 1; n >>= 1) {
+#pragma unroll
+        for (int i = 0; i < n; ++i) {
+            if (!FAITH) lo[i] = fmaxf(fminf(hi[i], hi[i + n]), fmaxf(lo[i], lo[i + n]));
+            hi[i] = fmaxf(hi[i], hi[i + n]);
+        }
+    }
+    const float mine_v = fmaxf(hi[0], 0.0f); // all-NaN -> 0
+    const unsigned full = 0xffffffffu;
+    Top r;
+    r.v = __uint_as_float(__reduce_max_sync(full, __float_as_uint(mine_v)));
+    const bool mine = mine_v == r.v && r.v > 0.0f; // a value that is not > 0 never wins: index 0
+    int cand = 0x7fffffff;
+    if (mine) {
+        // lowest bin holding the maximum: descending scan, the last hit is the lowest
+#pragma unroll
+        for (int e = Rp - 1; e >= 0; --e) {
+#pragma unroll
+            for (int g = Gp - 1; g >= 0; --g) {
+                const int i = g * Rp + e;
+                if (m2[i] == r.v) cand = bin_of<SF>(t, i);
+            }
+        }
+    }
+    r.i = __reduce_min_sync(full, cand);
+    if (r.i == 0x7fffffff) r.i = 0;
+    r.second = 0.0f;
+    if (!FAITH) {
+        const unsigned ties = __ballot_sync(full, mine);
+        const float x = mine ? fmaxf(lo[0], 0.0f) : mine_v;
+        r.second = __uint_as_float(__reduce_max_sync(full, __float_as_uint(x)));
+        if (__popc(ties) > 1) r.second = r.v;
+    }
+    if (TPW > 32) {
+        constexpr int WARPS = TPW / 32;
+        if ((t & 31) == 0) red[slot * WARPS + (t >> 5)] = r;
+        Group<TPW>::sync(slot);
+        if (t == 0) {
+            r = red[slot * WARPS];
+#pragma unroll
+            for (int w = 1; w < WARPS; ++w) r = top_merge(r, red[slot * WARPS + w]);
+        }
+    }
+    return r;
+}
+
 // ---- per-sample preparation -----------------------------------------------------------------------------------
 // Faithful: ((iq * down) * scale) * rot, then * window, each step rounded as phy.cpp:216-225 /
 // LoRaDemod.cpp:73-75,153-160 / tests/performance_test.cpp:109-114 round it.  `down` points at the entry of
@@ -143,14 +206,15 @@ struct PrepFast {
     const float* down_phase; // nullptr = no dechirp; else doubled table + down_ofs + t
     const float* window;     // nullptr or window + t
     float rate, base;
-    template <int OFS> PM_DEV c64 apply(c64 v) const
+    template <int OFS, bool WINDOWED> PM_DEV c64 apply(c64 v) const
     {
         float ph = fmaf(rate, (float)OFS, base);
         if (down_phase) ph += __ldg(down_phase + OFS);
         float sn, cs;
         __sincosf(ph, &sn, &cs);
         v = cmul<false>(v, pk(cs, sn), 1.0f);
-        if (window) v = cscale(v, __ldg(window + OFS));
+        // unconditional multiply where a window is possible: a select between two packed values costs two moves
+        if (WINDOWED) v = cscale(v, window ? __ldg(window + OFS) : 1.0f);
         return v;
     }
 };
@@ -204,8 +268,9 @@ PM_DEV WinParams window_params(const BlockedDemodArgs& a, const PktParams& k, in
 // A CTA of 256 threads holds 256/T window slots; each slot walks its own sequence of window chunks (a chunk =
 // `chunk` consecutive windows, normally of one packet, so the per-packet values are loaded once), and slots never
 // wait for each other (sub-warp / named-barrier synchronisation only).  LIST = window numbers come from the
-// recheck list instead of 0..n_windows-1.  OSR1 = oversampling ratio is 1 (every BASELINE config): sample
-// addresses become one pointer per window plus immediate offsets.
+// recheck list instead of 0..n_windows-1.  OSR1 = the common configuration, oversampling ratio 1 and no Hann
+// window (every BASELINE config): sample addresses become one pointer per window plus immediate offsets and
+// the window multiply disappears; the other instantiation handles any osr and an optional window.
 template <int SF>
 struct DemodCfg {
     static constexpr int T = Blk<SF>::T;
@@ -260,14 +325,14 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
                 st = fmaf(-kk, -1.74845553146951715e-7f, st);
                 const PrepFast prep{a.dechirp ? a.down_phase + q.down_ofs + t : nullptr, a.window ? a.window + t : nullptr,
                                     pk_.rate, fmaf(pk_.rate, (float)t, st)};
-                in[0] = prep.template apply<0 * T>(in[0]);   in[1] = prep.template apply<1 * T>(in[1]);
-                in[2] = prep.template apply<2 * T>(in[2]);   in[3] = prep.template apply<3 * T>(in[3]);
-                in[4] = prep.template apply<4 * T>(in[4]);   in[5] = prep.template apply<5 * T>(in[5]);
-                in[6] = prep.template apply<6 * T>(in[6]);   in[7] = prep.template apply<7 * T>(in[7]);
-                in[8] = prep.template apply<8 * T>(in[8]);   in[9] = prep.template apply<9 * T>(in[9]);
-                in[10] = prep.template apply<10 * T>(in[10]); in[11] = prep.template apply<11 * T>(in[11]);
-                in[12] = prep.template apply<12 * T>(in[12]); in[13] = prep.template apply<13 * T>(in[13]);
-                in[14] = prep.template apply<14 * T>(in[14]); in[15] = prep.template apply<15 * T>(in[15]);
+                in[0] = prep.template apply<0 * T, !OSR1>(in[0]);   in[1] = prep.template apply<1 * T, !OSR1>(in[1]);
+                in[2] = prep.template apply<2 * T, !OSR1>(in[2]);   in[3] = prep.template apply<3 * T, !OSR1>(in[3]);
+                in[4] = prep.template apply<4 * T, !OSR1>(in[4]);   in[5] = prep.template apply<5 * T, !OSR1>(in[5]);
+                in[6] = prep.template apply<6 * T, !OSR1>(in[6]);   in[7] = prep.template apply<7 * T, !OSR1>(in[7]);
+                in[8] = prep.template apply<8 * T, !OSR1>(in[8]);   in[9] = prep.template apply<9 * T, !OSR1>(in[9]);
+                in[10] = prep.template apply<10 * T, !OSR1>(in[10]); in[11] = prep.template apply<11 * T, !OSR1>(in[11]);
+                in[12] = prep.template apply<12 * T, !OSR1>(in[12]); in[13] = prep.template apply<13 * T, !OSR1>(in[13]);
+                in[14] = prep.template apply<14 * T, !OSR1>(in[14]); in[15] = prep.template apply<15 * T, !OSR1>(in[15]);
                 peak_scale = pk_.scale * pk_.scale;
                 // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
                 // the trusted margin widens with the magnitude of the phase
@@ -275,7 +340,7 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
                 margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
             }
             fft_blocked<SF, FAITH>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
-            Top best = group_top<T>(thread_top<SF, FAITH>(v, t), t, slot, red);
+            Top best = window_top<SF, FAITH, T>(v, t, slot, red);
             if (t == 0) {
                 if (!FAITH) {
                     const bool trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
@@ -329,6 +394,7 @@ __global__ void __launch_bounds__(kCta) prepass_blocked_kernel(const __grid_cons
     // In fused-dechirp mode the values examined are iq * down[n mod N] (performance_test.cpp:109-114).
     if (a.do_maxabs) {
         float mx = 0.0f;
+#pragma unroll 8
         for (size_t n = u; n < a.count; n += TPK) {
             c64 v = __ldg(x + n);
             if (a.dechirp) v = cmul<true>(v, __ldg(a.down + (n & (size_t)(N - 1))), a.one);
@@ -544,7 +610,7 @@ static cudaError_t launch_demod_osr(const BlockedDemodArgs& a, int precision, in
 template <int SF>
 static cudaError_t launch_demod_sf(const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
 {
-    return a.osr == 1 ? launch_demod_osr<SF, true>(a, precision, sm_count, st)
+    return (a.osr == 1 && a.window == nullptr) ? launch_demod_osr<SF, true>(a, precision, sm_count, st)
                       : launch_demod_osr<SF, false>(a, precision, sm_count, st);
 }
 
