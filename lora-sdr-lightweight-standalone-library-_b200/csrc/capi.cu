@@ -296,6 +296,7 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             BlockedDemodArgs da{};
             da.iq = pa.iq; da.packet_stride = packet_stride; da.count = count;
             da.n_windows = static_cast<unsigned>(pn * total);
+            da.n_packets = static_cast<unsigned>(pn);
             da.total = static_cast<int>(total);
             da.div_total = make_fastdiv(static_cast<unsigned>(total));
             da.osr = static_cast<int>(osr);

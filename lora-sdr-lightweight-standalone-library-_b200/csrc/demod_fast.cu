@@ -198,26 +198,25 @@ struct PrepFaith {
     }
 };
 
-// Fast: iq * exp(j*(down_phase[i] + start + rate*i)), then * window: dechirp and CFO rotation as ONE phase and
-// one MUFU sin/cos pair.  `base` = start (reduced to [-pi, pi]) + rate*t for this thread; sample j of the thread
-// is at in-window index t + T*j, so its phase is base + rate*(T*j) + down_phase[t + T*j].  The normalisation
-// scale is applied to the peak value instead (|X|^2 is homogeneous of degree 2).
-struct PrepFast {
-    const float* down_phase; // nullptr = no dechirp; else doubled table + down_ofs + t
-    const float* window;     // nullptr or window + t
-    float rate, base;
-    template <int OFS, bool WINDOWED> PM_DEV c64 apply(c64 v) const
-    {
-        float ph = fmaf(rate, (float)OFS, base);
-        if (down_phase) ph += __ldg(down_phase + OFS);
+// Fast flavour: dechirp and CFO rotation are one unit-modulus factor per sample,
+//     rot[i] = exp(j*(down_phase[ofs + i] + rate*i)),
+// and the window's start phase is dropped: it multiplies the whole window by one unit complex number, which
+// cannot change any |X[k]|^2.  rot[] therefore depends on the packet (rate) and on the table offset only, not on
+// the window, so each thread computes its 16 factors once per run of windows (one MUFU sin/cos pair each) and
+// keeps them in registers; per window a sample costs one fused complex multiply.  (Keeping them in shared memory
+// instead shrinks L1 below the twiddle table and was measured slower.)  The normalisation scale is applied to the peak value instead (|X|^2 is homogeneous of degree 2).
+template <int T>
+PM_DEV void compute_rotors(c64 (&rot)[16], const float* down_phase, float rate, int t)
+{
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        float ph = rate * (float)(t + T * j);
+        if (down_phase) ph += __ldg(down_phase + T * j);
         float sn, cs;
         __sincosf(ph, &sn, &cs);
-        v = cmul<false>(v, pk(cs, sn), 1.0f);
-        // unconditional multiply where a window is possible: a select between two packed values costs two moves
-        if (WINDOWED) v = cscale(v, window ? __ldg(window + OFS) : 1.0f);
-        return v;
+        rot[j] = pk(cs, sn);
     }
-};
+}
 
 // What every thread of a window needs to know about its packet and window (phy.cpp:197-214, LoRaDemod.cpp:137-151).
 struct PktParams {
@@ -289,20 +288,28 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
     const int slot = threadIdx.x / T;
     const int t = threadIdx.x % T;
     c64* S = smem + slot * B::WIN;
-    const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_windows;
+    const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_packets * a.chunks_per_packet;
     if (LIST && blockIdx.x == 0 && threadIdx.x == 0 && n_items) atomicAdd(a.stat_rechecked, (unsigned long long)n_items);
-    const unsigned chunk = LIST ? 1u : a.chunk;
-    const unsigned n_chunks = (n_items + chunk - 1) / chunk;
 
-    for (unsigned c = blockIdx.x * SLOTS + slot; c < n_chunks; c += gridDim.x * SLOTS) {
-        unsigned w = c * chunk;
-        const unsigned w_end = min(w + chunk, n_items);
-        unsigned wn = LIST ? a.flag_list[w] : w;
-        int p = a.div_total.d == 1 ? (int)wn : (int)(__umulhi(wn, a.div_total.magic) >> a.div_total.shift);
-        int s = (int)(wn - (unsigned)p * (unsigned)a.total);
-        PktParams pk_ = packet_params<SF>(a, p);
-        for (; w < w_end; ++w) {
+    for (unsigned c = blockIdx.x * SLOTS + slot; c < n_items; c += gridDim.x * SLOTS) {
+        int p, s, s_end;
+        if (LIST) { // one window, by number
+            const unsigned wn = a.flag_list[c];
+            p = a.div_total.d == 1 ? (int)wn : (int)(__umulhi(wn, a.div_total.magic) >> a.div_total.shift);
+            s = (int)(wn - (unsigned)p * (unsigned)a.total);
+            s_end = s + 1;
+        } else {    // a run of windows inside one packet
+            p = a.div_cpp.d == 1 ? (int)c : (int)(__umulhi(c, a.div_cpp.magic) >> a.div_cpp.shift);
+            s = (int)(c - (unsigned)p * a.chunks_per_packet) * (int)a.chunk_len;
+            s_end = min(s + (int)a.chunk_len, a.total);
+        }
+        const PktParams pk_ = packet_params<SF>(a, p);
+        const float peak_scale = pk_.scale * pk_.scale;
+        int rot_ofs = -1;
+        c64 rot[16];
+        for (; s < s_end; ++s) {
             const WinParams q = window_params<SF>(a, pk_, s);
+            const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
             const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
             c64 in[16], v[16];
             if (OSR1) {
@@ -313,27 +320,22 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
 #pragma unroll
                 for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
             }
-            float peak_scale = 1.0f, margin = 0.0f;
+            float margin = 0.0f;
             if (FAITH) {
                 const PrepFaith prep{a.dechirp ? a.down + q.down_ofs : nullptr, a.window, pk_.scale, true, pk_.rate, q.start, a.one};
 #pragma unroll
                 for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
             } else {
-                // start reduced to [-pi, pi] (Cody-Waite, two constants), so every phase stays below ~16 rad
-                const float kk = rintf(q.start * 0.15915494309189535f);
-                float st = fmaf(-kk, 6.28318548202514648f, q.start);
-                st = fmaf(-kk, -1.74845553146951715e-7f, st);
-                const PrepFast prep{a.dechirp ? a.down_phase + q.down_ofs + t : nullptr, a.window ? a.window + t : nullptr,
-                                    pk_.rate, fmaf(pk_.rate, (float)t, st)};
-                in[0] = prep.template apply<0 * T, !OSR1>(in[0]);   in[1] = prep.template apply<1 * T, !OSR1>(in[1]);
-                in[2] = prep.template apply<2 * T, !OSR1>(in[2]);   in[3] = prep.template apply<3 * T, !OSR1>(in[3]);
-                in[4] = prep.template apply<4 * T, !OSR1>(in[4]);   in[5] = prep.template apply<5 * T, !OSR1>(in[5]);
-                in[6] = prep.template apply<6 * T, !OSR1>(in[6]);   in[7] = prep.template apply<7 * T, !OSR1>(in[7]);
-                in[8] = prep.template apply<8 * T, !OSR1>(in[8]);   in[9] = prep.template apply<9 * T, !OSR1>(in[9]);
-                in[10] = prep.template apply<10 * T, !OSR1>(in[10]); in[11] = prep.template apply<11 * T, !OSR1>(in[11]);
-                in[12] = prep.template apply<12 * T, !OSR1>(in[12]); in[13] = prep.template apply<13 * T, !OSR1>(in[13]);
-                in[14] = prep.template apply<14 * T, !OSR1>(in[14]); in[15] = prep.template apply<15 * T, !OSR1>(in[15]);
-                peak_scale = pk_.scale * pk_.scale;
+                if (q.down_ofs != rot_ofs) { // first window of the run, or a window whose shift was not applied
+                    compute_rotors<T>(rot, a.dechirp ? a.down_phase + q.down_ofs + t : nullptr, pk_.rate, t);
+                    rot_ofs = q.down_ofs;
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    in[j] = cmul<false>(in[j], rot[j], 1.0f);
+                    // unconditional multiply where a window is possible: a select between packed values costs moves
+                    if (!OSR1) in[j] = cscale(in[j], a.window ? __ldg(a.window + t + T * j) : 1.0f);
+                }
                 // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
                 // the trusted margin widens with the magnitude of the phase
                 const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
@@ -356,10 +358,6 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
                 if (a.peaks) a.peaks[wn] = best.v;
             }
             Group<T>::sync(slot); // the window's exchange region (and red[]) is reused by the next iteration
-            if (!LIST) { // next window of the chunk
-                ++wn;
-                if (++s == a.total) { s = 0; ++p; if (w + 1 < w_end) pk_ = packet_params<SF>(a, p); }
-            }
         }
     }
 }
@@ -569,9 +567,10 @@ static cudaError_t launch_prepass_sf(const PrepassArgs& a, cudaStream_t st)
 }
 
 template <int SF, bool FAITH, bool LIST, bool OSR1>
-static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, unsigned items_hint, cudaStream_t st)
+static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, cudaStream_t st)
 {
     constexpr int SLOTS = DemodCfg<SF>::SLOTS;
+    // exchange regions, plus (fast flavour) 16 rotation factors per thread
     constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64;
     static int per_sm = 0;
     if (per_sm == 0) {
@@ -581,12 +580,23 @@ static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, unsigned i
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
     }
-    long long grid = (long long)sm_count * per_sm; // whole waves of resident CTAs; slots stride over the window chunks
-    // chunk: consecutive windows one slot takes at a time; at least ~8 chunks per slot for balance
+    long long grid = (long long)sm_count * per_sm; // whole waves of resident CTAs; slots stride over the work items
     const long long slots = grid * SLOTS;
-    long long chunk = (long long)items_hint / (slots * 8);
-    a.chunk = (unsigned)(chunk < 1 ? 1 : chunk > 16 ? 16 : chunk);
-    const long long need = ((long long)items_hint + (long long)SLOTS * a.chunk - 1) / ((long long)SLOTS * a.chunk);
+    long long items;
+    if (LIST) {
+        items = (long long)sm_count * SLOTS; // the list is short; its length is only known on the device
+    } else {
+        // cut every packet into runs of consecutive windows: as long as possible (the per-packet work is done once
+        // per run), but at least ~16 runs per slot so the slots finish together
+        long long cpp = (16 * slots + a.n_packets - 1) / a.n_packets;
+        if (cpp > a.total) cpp = a.total;
+        if (cpp < 1) cpp = 1;
+        a.chunk_len = (unsigned)((a.total + cpp - 1) / cpp);
+        a.chunks_per_packet = (unsigned)((a.total + a.chunk_len - 1) / a.chunk_len);
+        a.div_cpp = make_fastdiv(a.chunks_per_packet);
+        items = (long long)a.n_packets * a.chunks_per_packet;
+    }
+    const long long need = (items + SLOTS - 1) / SLOTS;
     if (grid > need) grid = need;
     if (grid < 1) grid = 1;
     demod_blocked_kernel<SF, FAITH, LIST, OSR1><<<(unsigned)grid, kCta, smem, st>>>(a);
@@ -597,14 +607,14 @@ static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, unsigned i
 template <int SF, bool OSR1>
 static cudaError_t launch_demod_osr(const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
 {
-    if (precision == PRECISION_EXACT) return launch_demod_one<SF, true, false, OSR1>(a, sm_count, a.n_windows, st);
+    if (precision == PRECISION_EXACT) return launch_demod_one<SF, true, false, OSR1>(a, sm_count, st);
     cudaError_t e = cudaMemsetAsync(a.flag_count, 0, sizeof(unsigned), st);
     if (e != cudaSuccess) return e;
-    e = launch_demod_one<SF, false, false, OSR1>(a, sm_count, a.n_windows, st);
+    e = launch_demod_one<SF, false, false, OSR1>(a, sm_count, st);
     if (e != cudaSuccess) return e;
     // the recheck list is short (about 1e-3 of the windows on noise); one CTA per SM is plenty, and the grid
     // size must not depend on a device-side count
-    return launch_demod_one<SF, true, true, OSR1>(a, sm_count, (unsigned)(sm_count * DemodCfg<SF>::SLOTS), st);
+    return launch_demod_one<SF, true, true, OSR1>(a, sm_count, st);
 }
 
 template <int SF>

@@ -35,7 +35,10 @@ struct BlockedDemodArgs {
     const c64* twp;         // per-stage twiddle table (Blk::toff): the values of kissfft.hh:24-29, regrouped
     const c64* down;        // reference down-chirp table (ChirpGenerator.hpp:24-50), stored twice back to back
     const float* down_phase; // phase of down[i] in radians in [-pi, pi], stored twice back to back
-    unsigned chunk;         // consecutive windows a slot takes at a time (set by the launcher)
+    // work split of the non-list kernels (set by the launcher): each packet is cut into chunks_per_packet runs of
+    // chunk_len consecutive windows, and a slot takes one run at a time
+    unsigned n_packets, chunk_len, chunks_per_packet;
+    FastDiv div_cpp;
     const float* window;    // Hann table or nullptr
     const float4* est;      // per packet: x = cfo, y = time_offset, z = scale, w = max_amp
     uint16_t* symbols;
