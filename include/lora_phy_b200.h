@@ -185,6 +185,14 @@ int lora_b200_estimate_host(lora_b200_ctx* ctx, const lora_b200_c32* h_iq, size_
 int lora_b200_modulate_host(lora_b200_ctx* ctx, const uint16_t* h_symbols, size_t symbol_count,
                             float amplitude, uint8_t sync, lora_b200_c32* h_iq, size_t iq_cap,
                             size_t* n_samples);
+/* lora_phy::encode / decode / compensate_offsets with host buffers (phy.cpp:55-63, 241-256, 147-176).  *produced is
+ * always set to the count the call yields (2*n_bytes, n_symbols/2); a too-small output buffer fails before anything
+ * is written.  compensate works in place on h_iq with the cfo / time_offset the caller holds in its metrics. */
+int lora_b200_encode_host(lora_b200_ctx* ctx, const uint8_t* h_bytes, size_t n_bytes, uint16_t* h_symbols,
+                          size_t symbol_cap, size_t* produced);
+int lora_b200_decode_host(lora_b200_ctx* ctx, const uint16_t* h_symbols, size_t n_symbols, uint8_t* h_bytes,
+                          size_t byte_cap, size_t* produced, int* crc_ok);
+int lora_b200_compensate_host(lora_b200_ctx* ctx, float cfo, float time_offset, lora_b200_c32* h_iq, size_t count);
 /* Batched host-buffer demod + chain decode: the end-to-end call bench.py times (pinned or pageable host
  * memory in, payloads and results out). */
 int lora_b200_receive_host(lora_b200_ctx* ctx, int mode, const lora_b200_chain_cfg* cfg,

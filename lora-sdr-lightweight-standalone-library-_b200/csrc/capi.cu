@@ -713,3 +713,77 @@ extern "C" int lora_b200_receive_host(lora_b200_ctx* c, int mode, const lora_b20
     CU(cudaStreamSynchronize(st));
     return LORA_B200_OK;
 }
+
+// ---- small host-buffer entry points used by include/lora_phy/phy.hpp -------------------------------------------
+extern "C" int lora_b200_encode_host(lora_b200_ctx* c, const uint8_t* h_bytes, size_t n_bytes, uint16_t* h_symbols,
+                                     size_t symbol_cap, size_t* produced)
+{
+    if (!c || !h_bytes || !h_symbols) return fail(LORA_B200_EINVAL, "null argument"); // phy.cpp:58
+    const size_t n_sym = 2 * n_bytes;
+    if (produced) *produced = n_sym;
+    if (n_sym > symbol_cap) return fail(LORA_B200_EINVAL, "symbol buffer too small");   // :61
+    if (n_bytes == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(c->s_misc.reserve(n_bytes));
+    CU(c->s_sym.reserve(sizeof(uint16_t) * n_sym));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_misc.p, h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
+    SimpleEncodeArgs a{c->s_misc.as<uint8_t>(), n_bytes, n_bytes, c->s_sym.as<uint16_t>(), n_sym, 1};
+    CU(launch_simple_encode(a, st));
+    CU(cudaMemcpyAsync(h_symbols, c->s_sym.p, sizeof(uint16_t) * n_sym, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_decode_host(lora_b200_ctx* c, const uint16_t* h_symbols, size_t n_symbols, uint8_t* h_bytes,
+                                     size_t byte_cap, size_t* produced, int* crc_ok)
+{
+    if (!c || !h_symbols || !h_bytes) return fail(LORA_B200_EINVAL, "null argument"); // phy.cpp:244
+    const size_t n_bytes = n_symbols / 2;
+    if (produced) *produced = n_bytes;
+    if (crc_ok) *crc_ok = 0;
+    if (n_bytes > byte_cap) return fail(LORA_B200_EINVAL, "payload buffer too small");  // :246 (checked before writing)
+    if (n_bytes == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(c->s_sym.reserve(sizeof(uint16_t) * n_symbols));
+    CU(c->s_misc.reserve(n_bytes + 16));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_sym.p, h_symbols, sizeof(uint16_t) * n_symbols, cudaMemcpyHostToDevice, st));
+    uint8_t* d_bytes = c->s_misc.as<uint8_t>();
+    SimpleDecodeArgs a{c->s_sym.as<uint16_t>(), n_symbols, n_symbols, d_bytes, n_bytes, d_bytes + n_bytes, 1};
+    CU(launch_simple_decode(a, st));
+    uint8_t flag = 0;
+    CU(cudaMemcpyAsync(h_bytes, d_bytes, n_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&flag, d_bytes + n_bytes, 1, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (crc_ok) *crc_ok = flag;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_compensate_host(lora_b200_ctx* c, float cfo, float time_offset, lora_b200_c32* h_iq, size_t count)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (!h_iq || count == 0) return LORA_B200_OK; // phy.cpp:150 silently returns
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(c->s_iq.reserve(sizeof(float2) * count));
+    CU(c->s_payload.reserve(sizeof(float2) * count));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count, cudaMemcpyHostToDevice, st));
+    CompensateArgs a{};
+    a.in = c->s_iq.as<float2>();
+    a.out = c->s_payload.as<float2>();
+    a.count = count;
+    // phy.cpp:156: -2*pi*cfo / (N*osr), left to right in float
+    volatile float num = -2.0f * 3.14159274101257324f * cfo;
+    volatile float den = static_cast<float>(c->n) * static_cast<float>(c->cfg.osr);
+    a.rate = num / den;
+    const long long off = static_cast<long long>(std::round(time_offset));                    // :163
+    a.offset = (off != 0 && static_cast<unsigned long long>(off < 0 ? -off : off) < count) ? off : 0; // :164,169
+    CU(launch_compensate(a, st));
+    CU(cudaMemcpyAsync(h_iq, a.out, sizeof(float2) * count, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return LORA_B200_OK;
+}

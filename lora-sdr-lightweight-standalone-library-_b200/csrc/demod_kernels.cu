@@ -279,8 +279,35 @@ __global__ void fill_est_kernel(float4* est, int n)
     if (p < n) est[p] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
 }
 
-// ---- launchers ---------------------------------------------------------------------------------------------
 unsigned long long g_launches = 0;
+
+// ---- compensate_offsets (phy.cpp:147-176) ---------------------------------------------------------------------------
+// The reference rotates in place and then moves the samples; out[n] is therefore rotated(in[n - offset]) where that
+// index exists and zero elsewhere.  cos/sin carry glibc's bits (exact_math.h), the product is std::complex's.
+__global__ void compensate_kernel(CompensateArgs a)
+{
+    const size_t n = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= a.count) return;
+    const long long m = (long long)n - a.offset;
+    float2 v = make_float2(0.0f, 0.0f);
+    if (m >= 0 && (size_t)m < a.count) {
+        const float ph = __fmul_rn(a.rate, (float)(size_t)m);
+        float sn, cs;
+        xm_sincosf(ph, &sn, &cs);
+        v = cmul_rn(a.in[m], make_float2(cs, sn));
+    }
+    a.out[n] = v;
+}
+
+cudaError_t launch_compensate(const CompensateArgs& a, cudaStream_t st)
+{
+    if (a.count == 0) return cudaSuccess;
+    compensate_kernel<<<(unsigned)((a.count + 255) / 256), 256, 0, st>>>(a);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
+// ---- launchers ---------------------------------------------------------------------------------------------
 
 cudaError_t launch_fill_est(float4* est, int n, cudaStream_t st)
 {

@@ -62,6 +62,15 @@ cudaError_t launch_maxabs(const MaxAbsArgs& a, int n_packets, cudaStream_t st);
 cudaError_t launch_estimate(int sf, const EstimateArgs& a, int n_packets, cudaStream_t st);
 cudaError_t launch_demod(int sf, const DemodArgs& a, int sm_count, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeArgs& a, cudaStream_t st);
+// compensate_offsets (phy.cpp:147-176): rotate sample n by rate*n, then shift by `offset` samples with zero fill.
+struct CompensateArgs {
+    const float2* in;
+    float2* out;
+    size_t count;
+    float rate;      // -2*pi*cfo / (N*osr), formed on the host in the reference's float order
+    long long offset; // round(time_offset); 0 when it would not be applied (|offset| >= count)
+};
+cudaError_t launch_compensate(const CompensateArgs& a, cudaStream_t st);
 cudaError_t launch_fill_est(float4* est, int n_packets, cudaStream_t st);
 
 extern unsigned long long g_launches; // kernels launched by this library (bench.py's gpu_launches)

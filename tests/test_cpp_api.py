@@ -1,0 +1,127 @@
+"""The reference's C++ API boundary (include/lora_phy/phy.hpp + liblora_phy.so) and its two drivers.
+
+bin/rx_runner and bin/tx_runner are the reference's own runners/rx_runner.cpp and tx_runner.cpp, compiled
+unmodified against this repo's headers and library (package Makefile).  On the GPU they must print / write exactly
+what the unmodified reference does (goldens made by scripts/make_golden.py and make_golden_runners.py); without a
+GPU they must fail loudly instead of computing anything on the CPU."""
+import hashlib
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "lora-sdr-lightweight-standalone-library-_b200")
+G = os.path.join(ROOT, "tests", "golden")
+RX, TX = os.path.join(PKG, "bin", "rx_runner"), os.path.join(PKG, "bin", "tx_runner")
+
+# every function include/lora_phy/phy.hpp declares, as g++ mangles it (reference phy.hpp:102-156,190-215)
+CPP_SYMBOLS = [
+    "_ZN8lora_phy4initEPNS_14lora_workspaceEPKNS_11lora_paramsE",
+    "_ZN8lora_phy5resetEPNS_14lora_workspaceE",
+    "_ZN8lora_phy6encodeEPNS_14lora_workspaceEPKhmPtm",
+    "_ZN8lora_phy6decodeEPNS_14lora_workspaceEPKtmPhm",
+    "_ZN8lora_phy8modulateEPNS_14lora_workspaceEPKtmPSt7complexIfEm",
+    "_ZN8lora_phy10demodulateEPNS_14lora_workspaceEPKSt7complexIfEmPtm",
+    "_ZN8lora_phy16estimate_offsetsEPNS_14lora_workspaceEPKSt7complexIfEm",
+    "_ZN8lora_phy18compensate_offsetsEPKNS_14lora_workspaceEPSt7complexIfEm",
+    "_ZN8lora_phy16get_last_metricsEPKNS_14lora_workspaceE",
+    "_ZN8lora_phy15lora_demod_initEPNS_20lora_demod_workspaceEjNS_11window_typeEPSt7complexIfEm",
+    "_ZN8lora_phy15lora_demod_freeEPNS_20lora_demod_workspaceE",
+    "_ZN8lora_phy13lora_modulateEPKtmPSt7complexIfEjjNS_9bandwidthEfh",
+    "_ZN8lora_phy15lora_demodulateEPNS_20lora_demod_workspaceEPKSt7complexIfEmPtjPh",
+    "_ZN8lora_phy11lora_encodeEPKhmPtj",
+    "_ZN8lora_phy11lora_decodeEPKtmPh",
+]
+
+
+def test_cpp_library_exports_the_reference_api():
+    lib = os.path.join(PKG, "liblora_phy.so")
+    assert os.path.exists(lib), "run __graft_entry__.build()"
+    names = subprocess.run(["nm", "-D", "--defined-only", lib], check=True, capture_output=True, text=True).stdout
+    for sym in CPP_SYMBOLS:
+        assert sym in names, sym
+
+
+@pytest.mark.skipif(not os.path.exists(RX), reason="runners are built only where the reference tree is present")
+def test_runners_fail_loudly_without_a_gpu(tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("this check is for the CPU-only container")
+    iq = np.zeros(256, np.complex64)
+    f = tmp_path / "z.iq"
+    iq.tofile(f)
+    r = subprocess.run([RX, f"--in={f}", "--sf=7"], capture_output=True, text=True)
+    assert r.returncode != 0 and "Payload" not in r.stdout
+    r = subprocess.run([TX, "--payload=deadbeef", "--sf=7", f"--out={tmp_path / 'o.iq'}"], capture_output=True, text=True)
+    assert r.returncode != 0
+
+
+needs_runners = pytest.mark.skipif(not os.path.exists(RX), reason="bin/rx_runner not built (no reference tree at build time)")
+
+
+@pytest.mark.gpu
+@needs_runners
+def test_rx_runner_config1_golden_capture(tmp_path):
+    """BASELINE configs[0]: stdout of the reference's rx_runner on the committed SF7 capture, byte for byte
+    (sha256 recorded in SURVEY.md F7)."""
+    g = np.load(os.path.join(G, "capture_sf7.npz"))
+    f = tmp_path / "capture.iq"
+    g["iq"].tofile(f)
+    out = subprocess.run([RX, f"--in={f}", "--sf=7", "--cr=1", "--bw=125000", "--report-offsets"], check=True,
+                         capture_output=True).stdout
+    assert out == g["rx_runner_stdout"].tobytes()
+    assert hashlib.sha256(out).hexdigest() == "91e55ba04aaff03239abd76229b6a6b13ec139f2e351439f92f87f726ac2cddb"
+
+
+@pytest.mark.gpu
+@needs_runners
+def test_tx_rx_runner_loopback_matches_reference(tmp_path):
+    """tx_runner writes the reference's IQ bit for bit, and rx_runner prints what the reference prints for it --
+    including the reference's own non-round-trip through demodulate()."""
+    g = np.load(os.path.join(G, "runners_loopback.npz"))
+    for k in range(3):
+        payload, sf, bw = (str(x) for x in g[f"case{k}_args"])
+        f = tmp_path / f"tx{k}.iq"
+        subprocess.run([TX, f"--payload={payload}", f"--sf={sf}", f"--bw={bw}", f"--out={f}"], check=True)
+        assert np.fromfile(f, np.complex64).tobytes() == g[f"case{k}_iq"].tobytes(), (k, "tx IQ differs")
+        out = subprocess.run([RX, f"--in={f}", f"--sf={sf}", f"--bw={bw}", "--report-offsets"], check=True,
+                             capture_output=True).stdout
+        assert out == g[f"case{k}_rx_stdout"].tobytes(), (k, out)
+
+
+PROFILES_YAML = """-
+  name: sf7_bw125_cr45
+  sf: 7
+  bw: 125000
+  cr: 4/5
+-
+  name: sf7_bw125_cr47
+  sf: 7
+  bw: 125000
+  cr: 4/7
+-
+  name: sf8_bw125_cr45
+  sf: 8
+  bw: 125000
+  cr: 4/5
+"""
+
+
+@pytest.mark.gpu
+@needs_runners
+@pytest.mark.parametrize("name", ["e2e_chain_test", "bit_exact_test", "roundtrip_test", "equal_power_bin_test",
+                                  "gr_lora_sdr_interop"])
+def test_reference_test_programs_pass_against_this_library(tmp_path, name):
+    """The reference's own tests/<name>.cpp, compiled unmodified against include/lora_phy and liblora_phy.so
+    (SURVEY.md section 4): encode -> lora_modulate -> caller dechirp -> lora_demodulate -> decode round trips for
+    the three profiles, the DEADBEEF known answers, the equal-power tie rule and the osr=2 interop capture."""
+    exe = os.path.join(PKG, "bin", "ref_" + name)
+    if not os.path.exists(exe):
+        pytest.skip("not built")
+    (tmp_path / "tests").mkdir()
+    (tmp_path / "tests" / "profiles.yaml").write_text(PROFILES_YAML)   # the three profiles of tests/profiles.yaml
+    np.load(os.path.join(G, "interop_sf7_osr2.npz"))["iq"].tofile(tmp_path / "test_output.iq")
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, (name, r.stdout[-400:], r.stderr[-400:])
