@@ -259,6 +259,7 @@ def main():
 
     import torch
     import lora_phy_b200 as L
+    from lora_phy_b200.shard import gather_records
     assert torch.cuda.is_available(), "bench.py needs a CUDA device; there is no CPU fallback"
     torch.cuda.set_device(local)
     dist = None
@@ -284,7 +285,7 @@ def main():
         wl.step(mode)
         if dist is not None:  # the only NVLink traffic: the decoded-record gather
             torch.cat([i["results"] for i in wl.items], out=res_cat)
-            dist.all_gather_into_tensor(gather_buf, res_cat)
+            gather_records(res_cat, dist, out=gather_buf)
 
     for _ in range(args.warmup):
         one_step()

@@ -80,6 +80,10 @@ _SIGNATURES = {
                                            C.c_float, C.c_uint8, C.c_void_p, C.c_size_t, C.c_void_p]),
     "lora_b200_awgn_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                        C.c_void_p, C.c_uint64, C.c_void_p]),
+    "lora_b200_encode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "lora_b200_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                        C.POINTER(C.c_int)]),
+    "lora_b200_compensate_host": (C.c_int, [C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_size_t]),
     "lora_b200_demodulate_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p,
                                             C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p]),
     "lora_b200_estimate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float),
@@ -291,6 +295,31 @@ class Context:
         _check(self.lib.lora_b200_estimate_host(self.h, samples.ctypes.data_as(C.c_void_p), len(samples),
                                                 C.byref(cfo), C.byref(to)))
         return np.float32(cfo.value), np.float32(to.value)
+
+    def compensate_offsets(self, cfo, time_offset, samples):
+        """lora_phy::compensate_offsets (phy.cpp:147-176) on a copy of `samples`."""
+        out = np.array(samples, np.complex64)
+        _check(self.lib.lora_b200_compensate_host(self.h, float(cfo), float(time_offset), out.ctypes.data_as(C.c_void_p),
+                                                  len(out)))
+        return out
+
+    def encode(self, payload):
+        """lora_phy::encode / lora_encode with host buffers -> uint16 symbols."""
+        payload = np.ascontiguousarray(payload, np.uint8)
+        out = np.zeros(2 * len(payload), np.uint16)
+        k = C.c_size_t()
+        _check(self.lib.lora_b200_encode_host(self.h, payload.ctypes.data_as(C.c_void_p), len(payload),
+                                              out.ctypes.data_as(C.c_void_p), len(out), C.byref(k)))
+        return out[:k.value]
+
+    def decode(self, symbols):
+        """lora_phy::decode with host buffers -> (bytes, crc_ok)."""
+        symbols = np.ascontiguousarray(symbols, np.uint16)
+        out = np.zeros(len(symbols) // 2, np.uint8)
+        k, ok = C.c_size_t(), C.c_int()
+        _check(self.lib.lora_b200_decode_host(self.h, symbols.ctypes.data_as(C.c_void_p), len(symbols),
+                                              out.ctypes.data_as(C.c_void_p), len(out), C.byref(k), C.byref(ok)))
+        return out[:k.value], bool(ok.value)
 
     def lora_modulate(self, symbols, amplitude=1.0, sync=0x12):
         symbols = np.ascontiguousarray(symbols, np.uint16)

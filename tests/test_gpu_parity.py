@@ -280,3 +280,25 @@ def test_fast_precision_filter(env, sf):
         rel = ((p1 - p0).abs() / p0).max().item()
         assert rel < 2e-5, (sf, mode, rel)
         assert windows == n_pk * (nsym + 2) and 0 < rechecked < 0.02 * windows, (sf, mode, windows, rechecked)
+
+
+def test_compensate_encode_decode_host_entry_points(env):
+    """compensate_offsets (phy.cpp:147-176) against the oracle in both shift directions and with a shift that is
+    too large to apply; encode / decode with host buffers against the oracle's Hamming(8,4) pairs and CRC flag."""
+    L, ORC, Params = env["L"], env["ORC"], env["Params"]
+    rng = np.random.default_rng(11)
+    for sf, osr in ((7, 1), (9, 2)):
+        ctx = L.Context(sf, osr=osr)
+        y = (rng.standard_normal(1000) + 1j * rng.standard_normal(1000)).astype(np.complex64)
+        for cfo, to in ((0.0, 0.0), (0.31, 5.4), (-0.07, -17.5), (0.5, 2000.0), (0.002, -999.4)):
+            got = ctx.compensate_offsets(cfo, to, y)
+            want = ORC.compensate_offsets(Params(sf, 125000, osr, 0, 0, 0x12), cfo, to, y)
+            assert bits(got) == bits(want), (sf, osr, cfo, to)
+    ctx = L.Context(7)
+    data = rng.integers(0, 256, 37, dtype=np.uint8)
+    sym = ctx.encode(data)
+    assert bits(sym) == bits(ORC.lora_encode(data))
+    sym[5] ^= 0x4  # one correctable bit error
+    out, ok = ctx.decode(sym)
+    o_out, o_ok = ORC.decode(sym)
+    assert bits(out) == bits(o_out) and ok == bool(o_ok)
