@@ -114,6 +114,9 @@ int lora_b200_kernel_time(lora_b200_ctx* ctx, double* total_ms, unsigned long lo
 #define LORA_B200_PRECISION_FAST 0
 #define LORA_B200_PRECISION_EXACT 1
 int lora_b200_set_precision(lora_b200_ctx* ctx, int precision);
+/* Large batches (>= 256 MB of IQ) are cut into 8 sub-batches whose prepass overlaps the previous sub-batch's demod
+ * kernel on internal streams; results do not depend on it.  enable = 0 runs everything on the caller's stream. */
+int lora_b200_set_overlap(lora_b200_ctx* ctx, int enable);
 /* Windows demodulated in FAST precision, and how many of them were rechecked, since the last call
  * (synchronises the device; for reporting only). */
 int lora_b200_recheck_stats(lora_b200_ctx* ctx, unsigned long long* windows, unsigned long long* rechecked);

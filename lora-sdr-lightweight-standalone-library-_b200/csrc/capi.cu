@@ -85,6 +85,11 @@ struct lora_b200_ctx {
     Buf s_iq, s_sym, s_metrics, s_payload, s_results, s_misc; // staging for the host-buffer entry points
     Buf h_pin;                   // pinned bounce buffer
     cudaStream_t stream = nullptr;
+    // prepass / demod pipeline of large batches: the scan+estimate of sub-batch k+1 runs beside the demod of k
+    cudaStream_t s_pre = nullptr, s_demod = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    std::vector<cudaEvent_t> ev_pre;
+    int overlap = 0;             // lora_b200_set_overlap (off by default: measured no faster)
     std::mutex mu;
     bool timing = false;                                     // lora_b200_set_kernel_timing
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool; // reused event pairs
@@ -142,6 +147,14 @@ extern "C" int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx**
               cudaMalloc(&c->d_stat_rechecked, sizeof(unsigned long long)) == cudaSuccess &&
               cudaMemset(c->d_stat_rechecked, 0, sizeof(unsigned long long)) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    if (ok) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        ok = cudaStreamCreateWithPriority(&c->s_pre, cudaStreamNonBlocking, hi) == cudaSuccess &&
+             cudaStreamCreateWithPriority(&c->s_demod, cudaStreamNonBlocking, lo) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->ev_begin, cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->ev_end, cudaEventDisableTiming) == cudaSuccess;
+    }
     if (ok && cfg->window == 1) ok = cudaMalloc(&c->d_window, sizeof(float) * c->n) == cudaSuccess;
     ok = ok && cudaMemcpy(c->d_tw, c->h_tw.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
          cudaMemcpy(c->d_down, c->h_down.data(), nb, cudaMemcpyHostToDevice) == cudaSuccess &&
@@ -171,6 +184,11 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
         b->release();
     for (auto& pr : c->ev_pool) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->s_pre) cudaStreamDestroy(c->s_pre);
+    if (c->s_demod) cudaStreamDestroy(c->s_demod);
+    if (c->ev_begin) cudaEventDestroy(c->ev_begin);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    for (cudaEvent_t e : c->ev_pre) cudaEventDestroy(e);
     delete c;
 }
 
@@ -208,6 +226,14 @@ extern "C" int lora_b200_set_precision(lora_b200_ctx* c, int precision)
         return fail(LORA_B200_EINVAL, "unknown precision");
     std::lock_guard<std::mutex> lk(c->mu);
     c->precision = precision;
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_set_overlap(lora_b200_ctx* c, int enable)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->overlap = enable != 0;
     return LORA_B200_OK;
 }
 
@@ -270,11 +296,31 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
     if (blocked_supported(static_cast<int>(c->cfg.sf))) {
         // SF7..SF12: register-blocked kernels (demod_fast.cu).  Batches are cut so that a launch sees < 2^31 windows.
         const int sf = static_cast<int>(c->cfg.sf);
-        const size_t chunk_packets = total ? std::max<size_t>(1, 0x7fffffffull / total) : n_packets;
+        size_t chunk_packets = total ? std::max<size_t>(1, 0x7fffffffull / total) : n_packets;
+        // Large batches are cut into 8 sub-batches and pipelined over two internal streams: the prepass (a DRAM-bound
+        // scan + two windows per packet) of sub-batch k+1 runs beside the demod kernel (issue-bound) of sub-batch k,
+        // which is launched with one CTA per SM fewer to leave room for it.
+        const bool pipelined = c->overlap && total > 0 && n_packets >= 64 &&
+                               n_packets * count * sizeof(float2) >= (size_t(256) << 20);
+        if (pipelined) chunk_packets = std::min(chunk_packets, (n_packets + 7) / 8);
+        const size_t n_sub = (n_packets + chunk_packets - 1) / chunk_packets;
         size_t max_windows = std::min(n_packets, chunk_packets) * total;
         if (total > 0 && c->precision == PRECISION_FAST) CU(c->flags.reserve(sizeof(unsigned) * (max_windows + 1)));
+        cudaStream_t st_pre = st, st_dem = st;
+        if (pipelined) {
+            while (c->ev_pre.size() < n_sub) {
+                cudaEvent_t e = nullptr;
+                CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                c->ev_pre.push_back(e);
+            }
+            st_pre = c->s_pre; st_dem = c->s_demod;
+            CU(cudaEventRecord(c->ev_begin, st));
+            CU(cudaStreamWaitEvent(st_pre, c->ev_begin, 0));
+            CU(cudaStreamWaitEvent(st_dem, c->ev_begin, 0));
+        }
         cudaEvent_t e0 = nullptr, e1 = nullptr;
-        for (size_t p0 = 0; p0 < n_packets; p0 += chunk_packets) {
+        size_t sub = 0;
+        for (size_t p0 = 0; p0 < n_packets; p0 += chunk_packets, ++sub) {
             const size_t pn = std::min(chunk_packets, n_packets - p0);
             PrepassArgs pa{};
             pa.iq = d_iq + p0 * packet_stride; pa.packet_stride = packet_stride; pa.count = count;
@@ -290,8 +336,12 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             pa.power_scale = c->power_scale;
             pa.est = est + p0;
             pa.tw0 = c->tw0; pa.one = 1.0f;
-            CU(launch_prepass_blocked(sf, pa, st));
+            CU(launch_prepass_blocked(sf, pa, st_pre));
             if (total == 0) continue;
+            if (pipelined) {
+                CU(cudaEventRecord(c->ev_pre[sub], st_pre));
+                CU(cudaStreamWaitEvent(st_dem, c->ev_pre[sub], 0));
+            }
 
             BlockedDemodArgs da{};
             da.iq = pa.iq; da.packet_stride = packet_stride; da.count = count;
@@ -315,6 +365,7 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             da.flag_list = c->flags.as<unsigned>() ? c->flags.as<unsigned>() + 1 : nullptr;
             da.flag_cap = da.n_windows;
             da.stat_rechecked = c->d_stat_rechecked;
+            da.max_ctas_per_sm = pipelined ? 2 : 0;
             if (c->timing) {
                 if (c->ev_used == c->ev_pool.size()) {
                     cudaEvent_t a = nullptr, b = nullptr;
@@ -325,11 +376,15 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
                 e0 = c->ev_pool[c->ev_used].first;
                 e1 = c->ev_pool[c->ev_used].second;
                 ++c->ev_used;
-                CU(cudaEventRecord(e0, st));
+                CU(cudaEventRecord(e0, st_dem));
             }
-            CU(launch_demod_blocked(sf, da, c->precision, c->sm_count, st));
-            if (c->timing) CU(cudaEventRecord(e1, st));
+            CU(launch_demod_blocked(sf, da, c->precision, c->sm_count, st_dem));
+            if (c->timing) CU(cudaEventRecord(e1, st_dem));
             if (c->precision == PRECISION_FAST) c->stat_windows += da.n_windows;
+        }
+        if (pipelined) {
+            CU(cudaEventRecord(c->ev_end, st_dem));
+            CU(cudaStreamWaitEvent(st, c->ev_end, 0));
         }
         if (d_metrics) {
             FinalizeArgs fa{est, c->sync_raw.as<uint16_t>(), d_metrics, np, static_cast<int>(c->cfg.sf),

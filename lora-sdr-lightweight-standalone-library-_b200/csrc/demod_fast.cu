@@ -372,7 +372,7 @@ struct PreCfg {
 };
 
 template <int SF>
-__global__ void __launch_bounds__(kCta) prepass_blocked_kernel(const __grid_constant__ PrepassArgs a)
+__global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ PrepassArgs a)
 {
     using B = Blk<SF>;
     constexpr int N = B::N, T = B::T, TPK = PreCfg<SF>::TPK, SLOTS = PreCfg<SF>::SLOTS;
@@ -392,14 +392,27 @@ __global__ void __launch_bounds__(kCta) prepass_blocked_kernel(const __grid_cons
     // In fused-dechirp mode the values examined are iq * down[n mod N] (performance_test.cpp:109-114).
     if (a.do_maxabs) {
         float mx = 0.0f;
-#pragma unroll 8
-        for (size_t n = u; n < a.count; n += TPK) {
-            c64 v = __ldg(x + n);
+        auto take = [&](c64 v, size_t n) {
             if (a.dechirp) v = cmul<true>(v, __ldg(a.down + (n & (size_t)(N - 1))), a.one);
             const float2 f = up(v);
             const float r = fabsf(f.x), im = fabsf(f.y);
             const float m = (r < im) ? im : r;
             if (m > mx) mx = m;
+        };
+        if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
+            // 16-byte aligned packet: two samples per load, eight loads in flight per thread (a max is order-free)
+            const ulonglong2* x2 = reinterpret_cast<const ulonglong2*>(x);
+            const size_t n2 = a.count >> 1;
+#pragma unroll 8
+            for (size_t i = u; i < n2; i += TPK) {
+                const ulonglong2 v = __ldg(x2 + i);
+                take(v.x, 2 * i);
+                take(v.y, 2 * i + 1);
+            }
+            if ((a.count & 1) && u == 0) take(__ldg(x + a.count - 1), a.count - 1);
+        } else {
+#pragma unroll 8
+            for (size_t n = u; n < a.count; n += TPK) take(__ldg(x + n), n);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) { const float y = __shfl_xor_sync(0xffffffffu, mx, o); if (y > mx) mx = y; }
@@ -580,7 +593,10 @@ static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, cudaStream
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
     }
-    long long grid = (long long)sm_count * per_sm; // whole waves of resident CTAs; slots stride over the work items
+    // whole waves of resident CTAs; slots stride over the work items.  max_ctas_per_sm leaves room on every SM for
+    // the prepass of the next sub-batch, which runs concurrently on another stream (capi.cu)
+    const int use = (a.max_ctas_per_sm > 0 && a.max_ctas_per_sm < per_sm) ? a.max_ctas_per_sm : per_sm;
+    long long grid = (long long)sm_count * use;
     const long long slots = grid * SLOTS;
     long long items;
     if (LIST) {

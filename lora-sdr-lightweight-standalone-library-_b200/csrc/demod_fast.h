@@ -52,6 +52,7 @@ struct BlockedDemodArgs {
     unsigned* flag_list;
     unsigned flag_cap;
     unsigned long long* stat_rechecked; // running total of rechecked windows (lora_b200_recheck_stats)
+    int max_ctas_per_sm;    // 0 = as many as fit; else a cap (room for a concurrent prepass)
 };
 
 struct PrepassArgs {

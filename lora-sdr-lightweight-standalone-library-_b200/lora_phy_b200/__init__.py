@@ -61,6 +61,7 @@ _SIGNATURES = {
     "lora_b200_set_kernel_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "lora_b200_kernel_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]),
     "lora_b200_set_precision": (C.c_int, [C.c_void_p, C.c_int]),
+    "lora_b200_set_overlap": (C.c_int, [C.c_void_p, C.c_int]),
     "lora_b200_recheck_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
     "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
@@ -153,6 +154,9 @@ class Context:
         """PRECISION_FAST (default): fused kernel + bit-faithful recheck of near-tie windows; PRECISION_EXACT:
         bit-faithful kernel on every window (peak values bit-identical too)."""
         _check(self.lib.lora_b200_set_precision(self.h, int(precision)))
+
+    def set_overlap(self, enable):
+        _check(self.lib.lora_b200_set_overlap(self.h, int(enable)))
 
     def recheck_stats(self):
         """-> (windows demodulated in FAST precision, windows rechecked) since the last call."""

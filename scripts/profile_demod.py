@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--packets", type=int, default=2048)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--precision", default="fast", choices=["fast", "exact"])
+    ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace", "legacy"])
     args = ap.parse_args()
     import torch
@@ -27,6 +28,7 @@ def main():
     sf = args.sf
     ctx = L.Context(sf)
     ctx.set_precision(L.PRECISION_FAST if args.precision == "fast" else L.PRECISION_EXACT)
+    ctx.set_overlap(not args.no_overlap)
     cfg = L.chain_cfg(sf, 1)
     gen = torch.Generator(device="cuda").manual_seed(sf)
     pay = torch.randint(0, 256, (args.packets, 16), dtype=torch.uint8, device="cuda", generator=gen)
