@@ -143,4 +143,12 @@ long   orc_chain_decode(const orc_chain_cfg* c, const uint16_t* symbols, size_t 
 #ifdef __cplusplus
 }
 #endif
+/* ---- stream.c: upstream Pothos blocks restated (LoRa-SDR/LoRaMod.cpp:109-238, LoRaDemod.cpp:98-327) ---------- */
+size_t orc_frame_modulate(unsigned sf, unsigned ovs, const uint16_t* symbols, size_t n_sym, unsigned char sync,
+                          unsigned padding, float ampl, orc_c32* out);
+void   orc_stream_tables(unsigned sf, orc_c32* up, orc_c32* down, orc_c32* fine);
+size_t orc_stream_demod(unsigned sf, unsigned char sync, float thresh, size_t mtu, const orc_c32* samples,
+                        size_t count, int16_t* out_symbols, size_t sym_cap, uint32_t* pkt_len, uint64_t* pkt_start,
+                        int32_t* pkt_err, size_t pkt_cap, uint64_t* consumed);
+
 #endif

@@ -217,6 +217,41 @@ class Lib:
         return int(r), out[:max(r, 0)], info
 
 
+    # ---- upstream Pothos blocks restated (oracle/stream.c) -------------------------------------------
+    def frame_modulate(self, sf, symbols, sync=0x12, padding=1, ampl=0.3, ovs=1):
+        symbols = np.ascontiguousarray(symbols, np.uint16)
+        f = self.fn("frame_modulate", C.c_size_t, [C.c_uint, C.c_uint, u16p, C.c_size_t, C.c_ubyte, C.c_uint,
+                                                   C.c_float, C.c_void_p])
+        n = f(sf, ovs, symbols, len(symbols), sync, padding, ampl, None)
+        out = np.zeros(n, np.complex64)
+        f(sf, ovs, symbols, len(symbols), sync, padding, ampl, out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def stream_tables(self, sf):
+        n = 1 << sf
+        up, down, fine = np.zeros(n, np.complex64), np.zeros(n, np.complex64), np.zeros(n * 128, np.complex64)
+        self.fn("stream_tables", None, [C.c_uint, c64p, c64p, c64p])(sf, up, down, fine)
+        return up, down, fine
+
+    def stream_demod(self, sf, samples, sync=0x12, thresh=-30.0, mtu=256, pkt_cap=64):
+        """-> (list of int16 symbol arrays, starts, freq errors, samples consumed)"""
+        samples = np.ascontiguousarray(samples, np.complex64)
+        sym = np.zeros(pkt_cap * mtu, np.int16)
+        plen, pstart, perr = np.zeros(pkt_cap, np.uint32), np.zeros(pkt_cap, np.uint64), np.zeros(pkt_cap, np.int32)
+        consumed = C.c_uint64()
+        n = self.fn("stream_demod", C.c_size_t, [C.c_uint, C.c_ubyte, C.c_float, C.c_size_t, c64p, C.c_size_t,
+                                                 C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                 C.c_size_t, C.POINTER(C.c_uint64)])(
+            sf, sync, thresh, mtu, samples, len(samples), sym.ctypes.data, len(sym), plen.ctypes.data,
+            pstart.ctypes.data, perr.ctypes.data, pkt_cap, C.byref(consumed))
+        n = min(n, pkt_cap)
+        pk, o = [], 0
+        for k in range(n):
+            pk.append(sym[o:o + plen[k]].copy())
+            o += int(plen[k])
+        return pk, pstart[:n].copy(), perr[:n].copy(), int(consumed.value)
+
+
 def chain_cfg(sf, rdd, ppm=0, explicit=True, crc=True, whitening=True, interleaving=True,
               error_check=False, hdr_out=False, data_length=8):
     return ChainCfg(sf, ppm, rdd, int(explicit), int(crc), int(whitening), int(interleaving),
