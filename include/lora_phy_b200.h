@@ -203,6 +203,46 @@ int lora_b200_receive_host(lora_b200_ctx* ctx, int mode, const lora_b200_chain_c
                            uint8_t* h_payload, lora_b200_chain_result* h_results,
                            lora_b200_pkt_metrics* h_metrics);
 
+/* ---- continuous-stream front end and full frames (upstream Pothos blocks) --------------------------------------
+ * LoRaDemod::work (LoRa-SDR/LoRaDemod.cpp:145-327): the frame synchroniser state machine -- 10-chirp preamble with
+ * fractional-bin fine tuning, two sync-word chirps, two down-chirps for the frequency error, the quarter chirp, then
+ * data symbols until `mtu` symbols or a squelched window -- run over n_streams independent sample streams (gateway
+ * channels, or segments of a long capture), one stream per group of N/16 threads.  osr must be 1 and sf 7..12.
+ * LoRaMod::work (LoRa-SDR/LoRaMod.cpp:109-238): the frame generator that produces such streams. */
+typedef struct lora_b200_stream_cfg {
+    uint8_t sync;          /* LoRaDemod::setSync, default 0x12 */
+    float thresh_db;       /* LoRaDemod::setThreshold, default -30 */
+    uint32_t mtu;          /* LoRaDemod::setMTU, default 256 */
+    uint32_t max_packets;  /* capacity of d_packets per stream */
+    uint32_t max_symbols;  /* capacity of d_symbols per stream */
+} lora_b200_stream_cfg;
+
+typedef struct lora_b200_stream_packet {
+    uint64_t start;        /* sample index (within the stream) of the first data window */
+    uint32_t first_symbol; /* offset of the packet's symbols in the stream's symbol region */
+    uint32_t n_symbols;
+    int32_t freq_error;    /* the "error" signal: averaged down-chirp bin error (:242-270) */
+    uint32_t reserved;
+} lora_b200_stream_packet;
+
+typedef struct lora_b200_stream_result {
+    uint64_t consumed;     /* samples consumed by the state machine */
+    uint32_t n_packets;    /* packets found; only the first max_packets are stored */
+    uint32_t n_symbols;    /* symbols stored (<= max_symbols) */
+} lora_b200_stream_result;
+
+/* Samples in one generated frame: (10 + 2 + 2 + n_symbols + padding) * N*osr + N*osr/4. */
+size_t lora_b200_frame_samples(const lora_b200_ctx* ctx, size_t n_symbols, unsigned padding);
+int lora_b200_frame_modulate_batch(lora_b200_ctx* ctx, const uint16_t* d_symbols, size_t n_packets, size_t n_symbols,
+                                   size_t symbol_stride, float amplitude, uint8_t sync, unsigned padding,
+                                   lora_b200_c32* d_iq, size_t packet_stride, void* stream);
+/* d_symbols: n_streams x max_symbols int16 (the reference's output packets carry int16 symbols, :297);
+ * d_packets: n_streams x max_packets; d_results: n_streams. */
+int lora_b200_stream_detect_batch(lora_b200_ctx* ctx, const lora_b200_stream_cfg* cfg, const lora_b200_c32* d_iq,
+                                  size_t n_streams, size_t samples_per_stream, size_t stream_stride,
+                                  int16_t* d_symbols, lora_b200_stream_packet* d_packets,
+                                  lora_b200_stream_result* d_results, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,6 +22,7 @@
 #include "demod_kernels.h"
 #include "host_tables.h"
 #include "mod_kernels.h"
+#include "stream_kernels.h"
 
 using namespace lora_b200;
 
@@ -81,6 +82,7 @@ struct lora_b200_ctx {
     unsigned long long stat_windows = 0; // windows demodulated in PRECISION_FAST since the last stats call
     unsigned long long* d_stat_rechecked = nullptr; // device-side running count of rechecked windows
     uint8_t* d_whiten = nullptr; // 2 x WHITEN_LEN bytes
+    float2* d_stream_tables = nullptr; // up (N), down (N), fine (128 N): built by the first stream_detect call
     Buf est, sync_raw;           // per-packet scratch of the demod kernels
     Buf s_iq, s_sym, s_metrics, s_payload, s_results, s_misc; // staging for the host-buffer entry points
     Buf h_pin;                   // pinned bounce buffer
@@ -179,6 +181,7 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
     cudaSetDevice(c->device);
     cudaFree(c->d_tw); cudaFree(c->d_down); cudaFree(c->d_window); cudaFree(c->d_whiten); cudaFree(c->d_down_phase); cudaFree(c->d_twp);
     cudaFree(c->d_stat_rechecked);
+    cudaFree(c->d_stream_tables);
     for (Buf* b : {&c->flags, &c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
                    &c->s_misc, &c->h_pin})
         b->release();
@@ -840,5 +843,94 @@ extern "C" int lora_b200_compensate_host(lora_b200_ctx* c, float cfo, float time
     CU(launch_compensate(a, st));
     CU(cudaMemcpyAsync(h_iq, a.out, sizeof(float2) * count, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    return LORA_B200_OK;
+}
+
+// ---- continuous-stream front end and full frames ---------------------------------------------------------------
+static_assert(sizeof(lora_b200_stream_packet) == sizeof(StreamPacket) && sizeof(lora_b200_stream_result) == sizeof(StreamResult),
+              "stream records must match the kernel's");
+
+extern "C" size_t lora_b200_frame_samples(const lora_b200_ctx* c, size_t n_symbols, unsigned padding)
+{
+    if (!c) return 0;
+    return frame_samples(static_cast<int>(c->cfg.sf), static_cast<int>(c->cfg.osr), n_symbols, padding);
+}
+
+extern "C" int lora_b200_frame_modulate_batch(lora_b200_ctx* c, const uint16_t* d_symbols, size_t n_packets,
+                                              size_t n_symbols, size_t symbol_stride, float amplitude, uint8_t sync,
+                                              unsigned padding, lora_b200_c32* d_iq, size_t packet_stride, void* stream)
+{
+    if (!c || !d_iq || (!d_symbols && n_symbols)) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_packets == 0) return LORA_B200_OK;
+    const size_t need = frame_samples(static_cast<int>(c->cfg.sf), static_cast<int>(c->cfg.osr), n_symbols, padding);
+    if (n_packets > 0x7fffffffu || packet_stride < need || symbol_stride < n_symbols || n_symbols > 0x7fffff00u)
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    FrameModArgs a{d_symbols, n_symbols, symbol_stride, reinterpret_cast<float2*>(d_iq), packet_stride,
+                   static_cast<int>(n_packets), static_cast<int>(c->cfg.sf), static_cast<int>(c->cfg.osr), amplitude, sync, padding};
+    CU(launch_frame_modulate(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_stream_cfg* cfg, const lora_b200_c32* d_iq,
+                                             size_t n_streams, size_t samples_per_stream, size_t stream_stride,
+                                             int16_t* d_symbols, lora_b200_stream_packet* d_packets,
+                                             lora_b200_stream_result* d_results, void* stream)
+{
+    if (!c || !cfg || !d_results) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_streams == 0) return LORA_B200_OK;
+    if (!d_iq || (!d_symbols && cfg->max_symbols) || (!d_packets && cfg->max_packets)) return fail(LORA_B200_EINVAL, "null argument");
+    if (c->cfg.osr != 1 || !blocked_supported(static_cast<int>(c->cfg.sf)))
+        return fail(LORA_B200_EINVAL, "stream detection needs osr 1 and sf 7..12 (LoRaDemod consumes N samples per symbol)");
+    if (n_streams > 0x7fffffffu || stream_stride < samples_per_stream) return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t n = static_cast<size_t>(c->n);
+    if (!c->d_stream_tables) {
+        std::vector<float2> up, down, fine;
+        build_stream_tables(static_cast<int>(c->cfg.sf), up, down, fine);
+        std::vector<float2> all(up);
+        all.insert(all.end(), down.begin(), down.end());
+        all.insert(all.end(), fine.begin(), fine.end());
+        CU(cudaMalloc(&c->d_stream_tables, sizeof(float2) * all.size()));
+        CU(cudaMemcpy(c->d_stream_tables, all.data(), sizeof(float2) * all.size(), cudaMemcpyHostToDevice));
+    }
+    StreamDetectArgs a{};
+    a.iq = reinterpret_cast<const float2*>(d_iq);
+    a.stream_stride = stream_stride;
+    a.count = samples_per_stream;
+    a.n_streams = static_cast<int>(n_streams);
+    a.twp = reinterpret_cast<const c64*>(c->d_twp);
+    a.tw0 = c->tw0;
+    a.one = 1.0f;
+    a.up = reinterpret_cast<const c64*>(c->d_stream_tables);
+    a.down = a.up + n;
+    a.fine = a.up + 2 * n;
+    a.power_scale = c->power_scale;
+    a.thresh = cfg->thresh_db;
+    a.mtu = cfg->mtu;
+    a.sync = cfg->sync;
+    a.symbols = d_symbols;
+    a.sym_cap = cfg->max_symbols;
+    a.packets = reinterpret_cast<StreamPacket*>(d_packets);
+    a.pkt_cap = cfg->max_packets;
+    a.results = reinterpret_cast<StreamResult*>(d_results);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c->timing) {
+        if (c->ev_used == c->ev_pool.size()) {
+            cudaEvent_t ea = nullptr, eb = nullptr;
+            CU(cudaEventCreate(&ea));
+            CU(cudaEventCreate(&eb));
+            c->ev_pool.emplace_back(ea, eb);
+        }
+        e0 = c->ev_pool[c->ev_used].first;
+        e1 = c->ev_pool[c->ev_used].second;
+        ++c->ev_used;
+        CU(cudaEventRecord(e0, st));
+    }
+    CU(launch_stream_detect(static_cast<int>(c->cfg.sf), a, c->sm_count, st));
+    if (e1) CU(cudaEventRecord(e1, st));
     return LORA_B200_OK;
 }

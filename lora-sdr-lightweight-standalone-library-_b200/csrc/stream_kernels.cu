@@ -1,0 +1,456 @@
+// stream_kernels.cu -- continuous-stream frame synchroniser (LoRa-SDR/LoRaDemod.cpp:145-327) and full-frame
+// generator (LoRa-SDR/LoRaMod.cpp:109-238).
+//
+// The synchroniser is a serial state machine per stream: how far the input advances depends on the bin detected
+// in the window just processed.  Parallelism therefore comes from (a) the T = N/16 threads that share each window
+// (dechirp, fine-tune rotation, bit-faithful FFT, peak search) and (b) many independent streams -- the gateway's
+// channels, or the segments a host cuts a long capture into -- one per slot of a persistent grid.
+// Every thread of a slot runs the state machine on identical inputs, so no decision needs broadcasting.
+#include "stream_kernels.h"
+
+#include <cmath>
+
+#include "demod_kernels.h" // g_launches
+#include "exact_math.h"
+#include "window_common.cuh"
+
+namespace lora_b200 {
+
+namespace {
+
+// ---- the fine-tune index walk ---------------------------------------------------------------------------------
+// LoRaDemod.cpp:157-165: per sample, an int index is converted to float, reduced by fine_err*128 (a float), truncated
+// back to int and wrapped once.  The rounding of the float subtraction depends on the binade of the index, so the
+// walk is piecewise arithmetic: constant stride inside a binade, with breaks at binade crossings, wraps and ties.
+// It is evaluated exactly without serialising it: guess an arithmetic progression from a known-correct start, let
+// every thread check "one exact step from my guessed index gives the next guessed index" for its own positions,
+// and accept the prefix before the first failed check (induction over positions).  The step after that prefix is
+// recomputed exactly and becomes the next start.  A round costs 16 exact steps per thread and one group minimum;
+// the number of rounds is the number of breaks (typically 1-3 per window).
+template <int N>
+PM_DEV int fine_step(int idx, float d)
+{
+    constexpr int W = N * STREAM_FINE_STEPS;
+    int r = __float2int_rz(__fsub_rn(__int2float_rn(idx), d));
+    if (r < 0) r += W;
+    else if (r >= W) r -= W;
+    // The reference indexes its table with whatever comes out (undefined behaviour once |d| >= W or d is NaN);
+    // here such an index is folded to 0 so the table read stays inside the allocation.
+    if ((unsigned)r >= (unsigned)W) r = 0;
+    return r;
+}
+
+template <int T>
+PM_DEV int group_min(int x, int t, int slot, int* scratch /* 2 * (T/32) ints per slot when T > 32 */, int round)
+{
+    if (T <= 32) {
+        const unsigned mask = Group<T>::mask();
+#pragma unroll
+        for (int o = T / 2; o > 0; o >>= 1) x = min(x, __shfl_xor_sync(mask, x, o));
+        return x;
+    } else {
+        constexpr int WARPS = T / 32;
+        x = __reduce_min_sync(0xffffffffu, x);
+        int* s = scratch + (slot * 2 + (round & 1)) * WARPS; // double-buffered: one barrier per round
+        if ((t & 31) == 0) s[t >> 5] = x;
+        Group<T>::sync(slot);
+        int r = s[0];
+#pragma unroll
+        for (int w = 1; w < WARPS; ++w) r = min(r, s[w]);
+        return r;
+    }
+}
+
+template <int SF>
+PM_DEV void fine_walk(int idx0, float fine_err, int t, int slot, int* scratch, int (&idx)[16], int& carry)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T, W = N * STREAM_FINE_STEPS;
+    const float d = __fmul_rn(fine_err, (float)STREAM_FINE_STEPS);
+    if (d == 0.0f) { // (int)((float)idx - 0) == idx
+#pragma unroll
+        for (int j = 0; j < 16; ++j) idx[j] = idx0;
+        carry = idx0;
+        return;
+    }
+    int base_pos = 0, base_idx = idx0;
+    for (int round = 0;; ++round) {
+        const unsigned s = (unsigned)(base_idx - fine_step<N>(base_idx, d)); // guessed stride, modulo 2^32 (W | 2^32)
+        int fail = N;
+        int guess[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int p = t + T * j;
+            const unsigned k = (unsigned)(p - base_pos);
+            const int h = (int)(((unsigned)base_idx - k * s) & (unsigned)(W - 1));
+            const int hn = (int)(((unsigned)h - s) & (unsigned)(W - 1));
+            guess[j] = h;
+            if (p >= base_pos && fine_step<N>(h, d) != hn) fail = min(fail, p);
+        }
+        const int pf = group_min<T>(fail, t, slot, scratch, round); // first position whose successor is not the guess
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int p = t + T * j;
+            if (p >= base_pos && p <= pf) idx[j] = guess[j];
+        }
+        if (pf >= N) { // every check passed, including the one at N-1 that validates position N
+            carry = (int)(((unsigned)base_idx - (unsigned)(N - base_pos) * s) & (unsigned)(W - 1));
+            return;
+        }
+        const int h_pf = (int)(((unsigned)base_idx - (unsigned)(pf - base_pos) * s) & (unsigned)(W - 1));
+        base_idx = fine_step<N>(h_pf, d);
+        base_pos = pf + 1;
+        if (base_pos >= N) { carry = base_idx; return; }
+    }
+}
+
+// ---- one window through the detector ---------------------------------------------------------------------------
+struct Det {
+    int value;
+    float power, power_avg, f_index;
+};
+
+template <int SF>
+struct StreamCfg {
+    static constexpr int T = Blk<SF>::T;
+    static constexpr int SLOTS = kCta / T;
+    static constexpr int SMEM_C64 = SLOTS * Blk<SF>::WIN;
+};
+
+struct SlotShared {
+    Top* red;        // kCta/32
+    double* redd;    // kCta/32
+    int* redi;       // 2 * kCta/32
+    float4* bc;      // per slot: (value bits, max bits, total lo, total hi)
+};
+
+template <int SF>
+PM_DEV Det detect_window(const StreamDetectArgs& a, const c64* __restrict__ x, const c64* __restrict__ chirp, int& ft,
+                         float fine_err, c64* S, const SlotShared& sh, int t, int slot)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T;
+    int idx[16];
+    int carry;
+    fine_walk<SF>(ft, fine_err, t, slot, sh.redi, idx, carry);
+    ft = carry;
+    c64 in[16], v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { // LoRaDemod.cpp:157-160: (samp * chirp) * fineTune, two rounded complex products
+        const c64 s = __ldg(x + t + T * j);
+        const c64 dc = cmul<true>(s, __ldg(chirp + t + T * j), a.one);
+        in[j] = cmul<true>(dc, __ldg(a.fine + idx[j]), a.one);
+    }
+    fft_blocked<SF, true>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
+    Top top = window_top<SF, true, T>(v, t, slot, sh.red);
+    // LoRaDetector.hpp:46-58 accumulates |X|^2 in a double, bin after bin; here the same doubles are added as a tree
+    // (per thread, then across the slot).  Each term has a 24-bit mantissa, so the double sum is exact -- and the
+    // order irrelevant -- unless the terms span more than 2^17 in magnitude; beyond that the two orders can differ in
+    // the last bits of the double, far below the float the total is narrowed to at :60.
+    double tot = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tot = __dadd_rn(tot, (double)mag2<true>(v[i]));
+    {
+        constexpr int Wd = T < 32 ? T : 32;
+        const unsigned mask = Group<T>::mask();
+#pragma unroll
+        for (int o = Wd / 2; o > 0; o >>= 1) tot = __dadd_rn(tot, __shfl_xor_sync(mask, tot, o));
+    }
+    Group<T>::sync(slot); // exchange loads done: the region now takes the natural-order spectrum
+#pragma unroll
+    for (int i = 0; i < 16; ++i) S[bin_of<SF>(t, i)] = v[i];
+    if (T > 32) {
+        constexpr int WARPS = T / 32;
+        if ((t & 31) == 0) sh.redd[slot * WARPS + (t >> 5)] = tot;
+        Group<T>::sync(slot);
+        if (t == 0) {
+            double sum = sh.redd[slot * WARPS];
+#pragma unroll
+            for (int w = 1; w < WARPS; ++w) sum = __dadd_rn(sum, sh.redd[slot * WARPS + w]);
+            sh.bc[slot] = make_float4(__int_as_float(top.i), top.v, __int_as_float(__double2loint(sum)),
+                                      __int_as_float(__double2hiint(sum)));
+        }
+        Group<T>::sync(slot);
+        const float4 b = sh.bc[slot];
+        top.i = __float_as_int(b.x);
+        top.v = b.y;
+        tot = __hiloint2double(__float_as_int(b.w), __float_as_int(b.z));
+    } else {
+        Group<T>::sync(slot);
+    }
+    Det r;
+    r.value = top.i;
+    // LoRaDetector.hpp:60-71
+    const float noise = __fsqrt_rn((float)__dsub_rn(tot, (double)top.v));
+    const float fundamental = __fsqrt_rn(top.v);
+    r.power_avg = __fsub_rn(__fmul_rn(20.0f, log10f(noise)), a.power_scale);
+    r.power = __fsub_rn(__fmul_rn(20.0f, log10f(fundamental)), a.power_scale);
+    const float2 Lb = up(S[top.i > 0 ? top.i - 1 : N - 1]);
+    const float2 Rb = up(S[top.i < N - 1 ? top.i + 1 : 0]);
+    const float left = xm_hypotf(Lb.x, Lb.y), right = xm_hypotf(Rb.x, Rb.y);
+    const double demon = __dsub_rn(__dsub_rn(__dmul_rn(2.0, (double)fundamental), (double)right), (double)left);
+    r.f_index = (demon == 0.0) ? 0.0f : (float)__ddiv_rn(__dmul_rn(0.5, (double)__fsub_rn(right, left)), demon);
+    Group<T>::sync(slot); // S is rewritten by the next window
+    return r;
+}
+
+enum { FRAMESYNC, DOWNCHIRP0, DOWNCHIRP1, QUARTERCHIRP, DATASYMBOLS };
+
+template <int SF>
+__global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_constant__ StreamDetectArgs a)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T, SLOTS = StreamCfg<SF>::SLOTS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ Top red[kCta / 32];
+    __shared__ double redd[kCta / 32];
+    __shared__ int redi[2 * (kCta / 32)];
+    __shared__ float4 bc[kCta / 8];
+    const int slot = threadIdx.x / T, t = threadIdx.x % T;
+    c64* S = reinterpret_cast<c64*>(smem_raw) + slot * B::WIN;
+    const SlotShared sh{red, redd, redi, bc};
+    const unsigned sync_hi = a.sync >> 4, sync_lo = a.sync & 0xfu;
+
+    // whole slots walk the streams; slots never synchronise with each other
+    for (int st = blockIdx.x * SLOTS + slot; st < a.n_streams; st += gridDim.x * SLOTS) {
+        const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)st * a.stream_stride;
+        int16_t* out = a.symbols + (size_t)st * a.sym_cap;
+        StreamPacket* pk_out = a.packets + (size_t)st * a.pkt_cap;
+        // activate(), LoRaDemod.cpp:138-142; _prevValue/_freqError/_finefreqError start at zero (the reference leaves
+        // them uninitialised, :68-75)
+        int state = FRAMESYNC;
+        const c64* chirp = a.up;
+        int fine_idx = 0, freq_err = 0;
+        float fine_err = 0.0f;
+        short prev_value = 0;
+        size_t pos = 0, cur_start = 0;
+        unsigned sym_count = 0, n_pkt = 0;
+        size_t sym_used = 0;
+
+        while (pos + 2 * (size_t)N <= a.count) { // :148
+            Det d = detect_window<SF>(a, x + pos, chirp, fine_idx, fine_err, S, sh, t, slot);
+            const unsigned value = (unsigned)d.value;
+            const bool squelched = __fsub_rn(d.power, d.power_avg) < a.thresh; // :174
+            size_t total = 0;
+            switch (state) {
+            case FRAMESYNC: { // :180-237
+                const bool syncd = !squelched && (prev_value + 4) / 8 == 0;
+                const bool match0 = (value + 4) / 8 == sync_hi;
+                bool match1 = false;
+                if (syncd && match0) {
+                    int ft = fine_idx; // the look-ahead walks a copy (:191-203) but overwrites power/powerAvg/fIndex (:204)
+                    d = detect_window<SF>(a, x + pos + N, chirp, ft, fine_err, S, sh, t, slot);
+                    match1 = ((unsigned)d.value + 4) / 8 == sync_lo;
+                }
+                if (syncd && match0 && match1) {
+                    total = 2 * (size_t)N;
+                    state = DOWNCHIRP0;
+                    chirp = a.down;
+                } else if (!squelched) {
+                    total = (size_t)N - value;
+                    fine_err = __fadd_rn(fine_err, d.f_index);
+                } else {
+                    total = N;
+                    fine_err = 0.0f;
+                    fine_idx = 0;
+                }
+            } break;
+            case DOWNCHIRP0: { // :242-250
+                state = DOWNCHIRP1;
+                total = N;
+                int error = (int)value;
+                if (value > (unsigned)N / 2) error -= N;
+                freq_err = error;
+            } break;
+            case DOWNCHIRP1: { // :255-270
+                state = QUARTERCHIRP;
+                total = N;
+                chirp = a.up;
+                int error = (int)value;
+                if (value > (unsigned)N / 2) error -= N;
+                freq_err = (freq_err + error) / 2;
+            } break;
+            case QUARTERCHIRP: { // :275-284
+                state = DATASYMBOLS;
+                total = (size_t)(N / 4) + (size_t)(long long)(freq_err / 2); // size_t + int, modulo 2^64 like the reference
+                fine_err = __fadd_rn(fine_err, (float)(freq_err / 2));
+                sym_count = 0;
+                cur_start = pos + total;
+            } break;
+            default: { // DATASYMBOLS, :289-310
+                total = N;
+                if (t == 0 && sym_used + sym_count < a.sym_cap) out[sym_used + sym_count] = (int16_t)value;
+                ++sym_count;
+                if (sym_count >= a.mtu || squelched) {
+                    if (t == 0 && n_pkt < a.pkt_cap) {
+                        StreamPacket p;
+                        p.start = cur_start;
+                        p.first_symbol = (uint32_t)sym_used;
+                        p.n_symbols = sym_count;
+                        p.freq_error = freq_err;
+                        p.reserved = 0;
+                        pk_out[n_pkt] = p;
+                    }
+                    ++n_pkt;
+                    sym_used += sym_count;
+                    if (sym_used > a.sym_cap) sym_used = a.sym_cap;
+                    fine_err = 0.0f;
+                    state = FRAMESYNC;
+                }
+            } break;
+            }
+            prev_value = (short)value; // :326
+            pos += total;              // :321
+        }
+        if (t == 0) {
+            StreamResult r;
+            r.consumed = pos;
+            r.n_packets = n_pkt;
+            r.n_symbols = (uint32_t)sym_used;
+            a.results[st] = r;
+        }
+    }
+}
+
+// ---- frame generator --------------------------------------------------------------------------------------------
+// Same layout as mod_kernels.cu: genChirp (LoRa-SDR/ChirpGenerator.hpp) is a serial float recurrence with the phase
+// carried through the whole frame, so a lane owns a frame for the recurrence and the warp shares the cos/sin work.
+constexpr int FM_CHUNK = 32;
+constexpr int FM_WARPS = 4;
+
+__global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModArgs a)
+{
+    __shared__ float ph[FM_WARPS][32][FM_CHUNK + 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int pk0 = (blockIdx.x * FM_WARPS + warp) * 32;
+    if (pk0 >= a.n_packets) return; // whole warp
+    const int pk = pk0 + lane;
+    const bool live = pk < a.n_packets;
+    const int N = 1 << a.sf;
+    const int NN = N * a.osr;
+    const double pi = 3.14159265358979323846;
+    const float f_min = (float)__ddiv_rn(-pi, (double)a.osr);
+    const float f_max = (float)__ddiv_rn(pi, (double)a.osr);
+    const float f_step = (float)__ddiv_rn(2 * pi, (double)(N * a.osr * a.osr));
+    const float span = __fsub_rn(f_max, f_min);
+    const uint16_t* sym = a.symbols + (size_t)(live ? pk : pk0) * a.symbol_stride;
+    const int segments = 15 + (int)a.n_symbols; // 10 up, 2 sync, 2 down, 1/4 down, data (LoRaMod.cpp:138-208)
+    const int warp_live = min(32, a.n_packets - pk0);
+
+    float phase = 0.0f; // :131
+    size_t at = 0;
+    for (int s = 0; s < segments; ++s) {
+        const bool down = s >= 12 && s < 15;
+        const int len = s == 14 ? NN / 4 : NN;
+        int v = 0;
+        if (s == 10) v = (int)(a.sync >> 4) * 8;          // :150
+        else if (s == 11) v = (int)(a.sync & 0xfu) * 8;   // :162
+        else if (s >= 15) v = sym[s - 15];                // :205
+        // freq = (2*M_PI*sym)/NN in double, narrowed to the float argument of genChirp
+        const float f0 = (float)__ddiv_rn(__dmul_rn(2 * pi, (double)v), (double)NN);
+        float f = __fadd_rn(f_min, f0);
+        for (int c0 = 0; c0 < len; c0 += FM_CHUNK) {
+            const int n = min(FM_CHUNK, len - c0);
+            for (int j = 0; j < n; ++j) {
+                f = __fadd_rn(f, f_step);
+                if (f > f_max) f = __fsub_rn(f, span);
+                phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
+                ph[warp][lane][j] = phase;
+            }
+            __syncwarp();
+            for (int q = 0; q < warp_live; ++q) {
+                if (lane < n) {
+                    float sn, cs;
+                    xm_sincosf(ph[warp][q][lane], &sn, &cs);
+                    a.iq[(size_t)(pk0 + q) * a.packet_stride + at + c0 + lane] =
+                        make_float2(__fmul_rn(a.amplitude, cs), __fmul_rn(a.amplitude, sn));
+                }
+            }
+            __syncwarp();
+        }
+        at += (size_t)len;
+        const double pd = (double)phase; // one wrap per chirp, in double
+        phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
+    }
+    // :224-226 zero padding
+    const size_t pad = (size_t)a.padding * NN;
+    for (int q = 0; q < warp_live; ++q)
+        for (size_t i = lane; i < pad; i += 32) a.iq[(size_t)(pk0 + q) * a.packet_stride + at + i] = make_float2(0.0f, 0.0f);
+}
+
+template <int SF>
+cudaError_t launch_stream_sf(const StreamDetectArgs& a, int sm_count, cudaStream_t st)
+{
+    constexpr int SLOTS = StreamCfg<SF>::SLOTS;
+    const size_t smem = sizeof(c64) * StreamCfg<SF>::SMEM_C64;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(stream_detect_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, stream_detect_kernel<SF>, kCta, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    int grid = (a.n_streams + SLOTS - 1) / SLOTS;
+    if (grid > sm_count * per_sm) grid = sm_count * per_sm;
+    if (grid < 1) grid = 1;
+    stream_detect_kernel<SF><<<grid, kCta, smem, st>>>(a);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
+} // namespace
+
+void build_stream_tables(int sf, std::vector<float2>& up, std::vector<float2>& down, std::vector<float2>& fine)
+{
+    const size_t n = (size_t)1 << sf;
+    up.resize(n);
+    down.resize(n);
+    fine.resize(n * STREAM_FINE_STEPS);
+    float phase = (float)(-M_PI); // LoRaDemod.cpp:99
+    double accum = 0.0;
+    for (size_t i = 0; i < n; ++i) {
+        accum += phase;
+        const double c = std::cos(accum), s = std::sin(accum); // std::polar(1.0, accum)
+        up[i] = make_float2((float)c, (float)(-s));
+        down[i] = make_float2((float)c, (float)s);
+        phase = (float)((double)phase + (2 * M_PI) / (double)n);
+    }
+    accum = 0.0;
+    phase = (float)(2.0 * M_PI / (double)(n * STREAM_FINE_STEPS)); // :111
+    for (size_t i = 0; i < n * STREAM_FINE_STEPS; ++i) {
+        accum += phase;
+        fine[i] = make_float2((float)std::cos(accum), (float)std::sin(accum));
+    }
+}
+
+size_t frame_samples(int sf, int osr, size_t n_symbols, unsigned padding)
+{
+    const size_t nn = ((size_t)1 << sf) * (size_t)osr;
+    return 14 * nn + nn / 4 + n_symbols * nn + (size_t)padding * nn;
+}
+
+cudaError_t launch_stream_detect(int sf, const StreamDetectArgs& a, int sm_count, cudaStream_t st)
+{
+    switch (sf) {
+    case 7: return launch_stream_sf<7>(a, sm_count, st);
+    case 8: return launch_stream_sf<8>(a, sm_count, st);
+    case 9: return launch_stream_sf<9>(a, sm_count, st);
+    case 10: return launch_stream_sf<10>(a, sm_count, st);
+    case 11: return launch_stream_sf<11>(a, sm_count, st);
+    case 12: return launch_stream_sf<12>(a, sm_count, st);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+cudaError_t launch_frame_modulate(const FrameModArgs& a, cudaStream_t st)
+{
+    const int per_block = 32 * FM_WARPS;
+    frame_modulate_kernel<<<(a.n_packets + per_block - 1) / per_block, per_block, 0, st>>>(a);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
+} // namespace lora_b200

@@ -41,6 +41,17 @@ CHAIN_RESULT = np.dtype([("n_bytes", "<i2"), ("drop_line", "<i2"), ("parity_erro
 assert PKT_METRICS.itemsize == 16 and CHAIN_RESULT.itemsize == 16
 
 
+class StreamCfg(C.Structure):  # lora_b200_stream_cfg
+    _fields_ = [("sync", C.c_uint8), ("thresh_db", C.c_float), ("mtu", C.c_uint32), ("max_packets", C.c_uint32),
+                ("max_symbols", C.c_uint32)]
+
+
+# lora_b200_stream_packet / lora_b200_stream_result as numpy record layouts
+STREAM_PACKET = np.dtype([("start", "<u8"), ("first_symbol", "<u4"), ("n_symbols", "<u4"), ("freq_error", "<i4"),
+                          ("reserved", "<u4")])
+STREAM_RESULT = np.dtype([("consumed", "<u8"), ("n_packets", "<u4"), ("n_symbols", "<u4")])
+
+
 class LoraB200Error(RuntimeError):
     pass
 
@@ -93,6 +104,11 @@ _SIGNATURES = {
                                           C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "lora_b200_receive_host": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
                                          C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_frame_samples": (C.c_size_t, [C.c_void_p, C.c_size_t, C.c_uint]),
+    "lora_b200_frame_modulate_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float,
+                                                 C.c_uint8, C.c_uint, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "lora_b200_stream_detect_batch": (C.c_int, [C.c_void_p, C.POINTER(StreamCfg), C.c_void_p, C.c_size_t, C.c_size_t,
+                                                C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 EXPORTS = tuple(_SIGNATURES)
 
@@ -258,6 +274,35 @@ class Context:
                                                  sync, _ptr(out), out.stride(0), _stream()))
         return out
 
+    # ---- continuous streams and full frames (LoRa-SDR/LoRaMod.cpp:109-238, LoRaDemod.cpp:145-327) ----------
+    def frame_samples(self, n_symbols, padding=0):
+        return self.lib.lora_b200_frame_samples(self.h, n_symbols, padding)
+
+    def frame_modulate_batch(self, symbols, amplitude=1.0, sync=0x12, padding=0, out=None):
+        """One full frame per row of `symbols`: preamble, sync word, down-chirps, data, zero padding."""
+        import torch
+        n, nsym = symbols.shape
+        count = self.frame_samples(nsym, padding)
+        if out is None:
+            out = torch.zeros((n, count), dtype=torch.complex64, device=symbols.device)
+        _check(self.lib.lora_b200_frame_modulate_batch(self.h, _ptr(symbols), n, nsym, symbols.stride(0), amplitude, sync,
+                                                       padding, _ptr(out), out.stride(0), _stream()))
+        return out
+
+    def stream_detect_batch(self, iq, sync=0x12, thresh_db=-30.0, mtu=256, max_packets=8, max_symbols=1024):
+        """LoRaDemod::work over every row of `iq` (streams x samples).  -> (symbols int16 [streams, max_symbols],
+        packets uint8 [streams, max_packets, 24] (view with STREAM_PACKET), results uint8 [streams, 16] (STREAM_RESULT))."""
+        import torch
+        n, count = iq.shape
+        sym = torch.zeros((n, max_symbols), dtype=torch.int16, device=iq.device)
+        pk = torch.zeros((n, max_packets, STREAM_PACKET.itemsize), dtype=torch.uint8, device=iq.device)
+        res = torch.zeros((n, STREAM_RESULT.itemsize), dtype=torch.uint8, device=iq.device)
+        cfg = StreamCfg(sync, thresh_db, mtu, max_packets, max_symbols)
+        stride = iq.stride(0) if n > 1 else max(iq.stride(0), count)  # a size-1 dimension may report any stride
+        _check(self.lib.lora_b200_stream_detect_batch(self.h, C.byref(cfg), _ptr(iq), n, count, stride, _ptr(sym),
+                                                      _ptr(pk), _ptr(res), _stream()))
+        return sym, pk, res
+
     def awgn_batch(self, iq, snr_db, seed=0):
         n, count = iq.shape
         _check(self.lib.lora_b200_awgn_batch(self.h, _ptr(iq), n, count, iq.stride(0), _ptr(snr_db), seed, _stream()))
@@ -345,6 +390,14 @@ class Context:
                                                payload.ctypes.data_as(C.c_void_p), results.ctypes.data_as(C.c_void_p),
                                                metrics.ctypes.data_as(C.c_void_p)))
         return payload, results, metrics
+
+
+def stream_records(packets, results):
+    """Device tensors of stream_detect_batch -> numpy record arrays (packets [streams, max_packets], results [streams])."""
+    p = packets.cpu().numpy()
+    r = results.cpu().numpy()
+    return (p.reshape(p.shape[0], -1).view(STREAM_PACKET).reshape(p.shape[0], p.shape[1]),
+            r.reshape(r.shape[0], -1).view(STREAM_RESULT).reshape(r.shape[0]))
 
 
 def metrics_to_numpy(t):
