@@ -115,6 +115,17 @@ PM_DEV WinParams window_params(const BlockedDemodArgs& a, const PktParams& k, in
     return q;
 }
 
+// One instruction asks the memory system to pull [p, p + bytes) into L2 (16-byte granules that lie fully inside the
+// range).  Issued by one thread per window for the window AFTER the one being loaded: by the time its samples are
+// wanted they come from L2 instead of HBM, without holding registers, shared memory or a barrier for them.
+PM_DEV void l2_prefetch(const void* p, size_t bytes)
+{
+    const unsigned long long a = (unsigned long long)p;
+    const unsigned long long lo = (a + 15ull) & ~15ull, hi = (a + bytes) & ~15ull;
+    if (hi > lo)
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((unsigned)(hi - lo)) : "memory");
+}
+
 // ---- the hot kernel ---------------------------------------------------------------------------------------------
 // A CTA of 256 threads holds 256/T window slots; each slot walks its own sequence of window chunks (a chunk =
 // `chunk` consecutive windows, normally of one packet, so the per-packet values are loaded once), and slots never
@@ -163,6 +174,11 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
             const WinParams q = window_params<SF>(a, pk_, s);
             const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
             const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
+            if (!LIST && t == 0) { // the samples right after this window: the next window of the run, or of the packet
+                const size_t span = (size_t)N * a.osr;
+                const size_t left = a.count - min(a.count, q.base + span);
+                l2_prefetch(x + span, sizeof(c64) * min(span, left));
+            }
             c64 in[16], v[16];
             if (OSR1) {
                 const c64* xt = x + t;
@@ -209,7 +225,10 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
                 else a.sync_raw[2 * (size_t)p + s] = (uint16_t)best.i;
                 if (a.peaks) a.peaks[wn] = best.v;
             }
-            Group<T>::sync(slot); // the window's exchange region (and red[]) is reused by the next iteration
+            // No barrier here.  The peak search is itself a rendezvous of the window's threads that comes after every
+            // thread's last exchange load (warp shuffles / REDUX for T <= 32, the barrier inside window_top for
+            // T > 32), so the exchange region is already free; and red[] is not written again before the next
+            // window's first barrier, which thread 0 only reaches after it has read red[] here.
         }
     }
 }
