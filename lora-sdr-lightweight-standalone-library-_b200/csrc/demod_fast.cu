@@ -148,6 +148,7 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
     extern __shared__ __align__(16) unsigned char smem_raw[];
     c64* smem = reinterpret_cast<c64*>(smem_raw);
     __shared__ Top red[T > 32 ? kCta / 32 : 1];
+    __shared__ float redw[T > 32 ? 2 * (kCta / 32) : 1];
     const int slot = threadIdx.x / T;
     const int t = threadIdx.x % T;
     c64* S = smem + slot * B::WIN;
@@ -210,8 +211,17 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
                 margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
             }
             fft_blocked<SF, FAITH>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
-            Top best = window_top<SF, FAITH, T>(v, t, slot, red);
-            if (t == 0) {
+            Top best{0.0f, 0, 0.0f};
+            bool owner; // the thread that reports this window
+            // measured: the winner-reports search is faster for windows of 2 or 4 warps (SF10 +3.6 %, SF11 +5 %) and
+            // slower for one warp (every warp takes the winner branch) and for eight (SF12 -6 %, longer barrier tail)
+            if (!FAITH && (T == 64 || T == 128)) {
+                owner = window_top_fast<SF, (T >= 32 ? T : 32)>(v, t, slot, redw, best);
+            } else {
+                best = window_top<SF, FAITH, T>(v, t, slot, red);
+                owner = t == 0;
+            }
+            if (owner) {
                 if (!FAITH) {
                     const bool trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
                     best.v *= peak_scale;

@@ -157,5 +157,85 @@ PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red)
     return r;
 }
 
+// Peak of one window for the fused-math flavour, TPW >= 32.  Every thread only finds the largest of its 16 values;
+// REDUX gives the warp's largest and the largest among the OTHER lanes; for windows spread over several warps one
+// round through shared memory (two floats per warp) gives every thread the window's maximum.  Only the thread that
+// holds that maximum then looks for the bin index and for the runner-up inside its own 16 values -- a branch that is
+// taken by one thread per window -- and that thread, not thread 0, reports the window.  Returns true in the
+// reporting thread(s).  Exact ties between threads make each of them report with second == max, i.e. untrusted:
+// the bit-faithful recheck then settles the lowest-index rule (a duplicate entry in the recheck list is harmless).
+template <int SF, int TPW>
+PM_DEV bool window_top_fast(const c64 (&v)[16], int t, int slot, float* redw /* 2 * kCta/32 */, Top& out)
+{
+    static_assert(TPW >= 32, "sub-warp windows use group_top");
+    using B = Blk<SF>;
+    constexpr int P = B::NP - 1, Rp = B::R(P), Gp = B::G(P), WARPS = TPW / 32;
+    const unsigned full = 0xffffffffu;
+    float m2[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) m2[i] = mag2<false>(v[i]);
+    float h8[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) h8[i] = fmaxf(m2[2 * i], m2[2 * i + 1]);
+    const float hi = fmaxf(fmaxf(fmaxf(fmaxf(h8[0], h8[1]), fmaxf(h8[2], h8[3])), fmaxf(fmaxf(h8[4], h8[5]), fmaxf(h8[6], h8[7]))), 0.0f);
+    const float wmax = __uint_as_float(__reduce_max_sync(full, __float_as_uint(hi)));
+    const bool top_lane = hi == wmax;
+    const unsigned lanes = __ballot_sync(full, top_lane);
+    float w2 = __uint_as_float(__reduce_max_sync(full, top_lane ? 0u : __float_as_uint(hi)));
+    if (__popc(lanes) > 1) w2 = wmax;
+    float M = wmax, other = w2;
+    float wm[WARPS], ws[WARPS];
+    if (WARPS > 1) {
+        float* rm = redw + slot * 2 * WARPS; // [0, WARPS): warp maxima, [WARPS, 2*WARPS): warp runners-up
+        if ((t & 31) == 0) { rm[t >> 5] = wmax; rm[WARPS + (t >> 5)] = w2; }
+        Group<TPW>::sync(slot);
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) wm[w] = rm[w];
+        M = wm[0];
+#pragma unroll
+        for (int w = 1; w < WARPS; ++w) M = fmaxf(M, wm[w]);
+    }
+    const bool winner = top_lane && hi == M && M > 0.0f; // a value that is not > 0 never wins
+    if (winner) {
+        if (WARPS > 1) {
+            const float* rm = redw + slot * 2 * WARPS;
+            int holders = 0;
+            other = 0.0f;
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) {
+                ws[w] = rm[WARPS + w];
+                const bool holds = wm[w] == M;
+                holders += holds ? 1 : 0;
+                other = fmaxf(other, holds ? ws[w] : wm[w]);
+            }
+            if (holders > 1) other = M;
+        }
+        int idx = 0, dup = 0;
+        float lo = 0.0f;
+        // descending scan over this thread's bins: the last hit is the lowest bin holding the maximum
+#pragma unroll
+        for (int e = Rp - 1; e >= 0; --e) {
+#pragma unroll
+            for (int g = Gp - 1; g >= 0; --g) {
+                const int i = g * Rp + e;
+                const bool hit = m2[i] == M;
+                if (hit) { idx = bin_of<SF>(t, i); ++dup; }
+                else lo = fmaxf(lo, m2[i]);
+            }
+        }
+        out.v = M;
+        out.i = idx;
+        out.second = dup > 1 ? M : fmaxf(other, lo);
+        return true;
+    }
+    if (t == 0 && !(M > 0.0f)) { // all-zero / all-NaN window: index 0, never trusted
+        out.v = M;
+        out.i = 0;
+        out.second = M;
+        return true;
+    }
+    return false;
+}
+
 } // namespace
 } // namespace lora_b200
