@@ -16,6 +16,8 @@
 //                             are exact under PRECISION_EXACT and within 1e-4 relative under PRECISION_FAST.
 #include "demod_fast.h"
 
+#include <type_traits>
+
 #include "demod_kernels.h"
 #include "exact_math.h"
 #include "window_common.cuh"
@@ -261,6 +263,7 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
     c64* smem = reinterpret_cast<c64*>(smem_raw);
     __shared__ Top red[kCta / 32];
     __shared__ float redf[kCta / 32];
+    __shared__ int redp[kCta / 32];
     const int slot = threadIdx.x / TPK;
     const int u = threadIdx.x % TPK;
     c64* S = smem + slot * B::WIN;
@@ -273,6 +276,9 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
     // In fused-dechirp mode the values examined are iq * down[n mod N] (performance_test.cpp:109-114).
     if (a.do_maxabs) {
         float mx = 0.0f;
+        const bool aligned = (reinterpret_cast<uintptr_t>(x) & 15u) == 0;
+        // Exact form: the reference's two comparisons per sample, so a NaN real part drops the sample and a NaN
+        // imaginary part drops only itself.
         auto take = [&](c64 v, size_t n) {
             if (a.dechirp) v = cmul<true>(v, __ldg(a.down + (n & (size_t)(N - 1))), a.one);
             const float2 f = up(v);
@@ -280,29 +286,90 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
             const float m = (r < im) ? im : r;
             if (m > mx) mx = m;
         };
-        if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
-            // 16-byte aligned packet: two samples per load, eight loads in flight per thread (a max is order-free)
-            const ulonglong2* x2 = reinterpret_cast<const ulonglong2*>(x);
-            const size_t n2 = a.count >> 1;
+        auto scan_exact = [&](size_t first) {
+            if (aligned && (first & 1) == 0) {
+                // 16-byte aligned: two samples per load, eight loads in flight per thread (a max is order-free)
+                const ulonglong2* x2 = reinterpret_cast<const ulonglong2*>(x);
+                const size_t n2 = a.count >> 1;
 #pragma unroll 8
-            for (size_t i = u; i < n2; i += TPK) {
-                const ulonglong2 v = __ldg(x2 + i);
-                take(v.x, 2 * i);
-                take(v.y, 2 * i + 1);
+                for (size_t i = (first >> 1) + u; i < n2; i += TPK) {
+                    const ulonglong2 v = __ldg(x2 + i);
+                    take(v.x, 2 * i);
+                    take(v.y, 2 * i + 1);
+                }
+                if ((a.count & 1) && u == 0) take(__ldg(x + a.count - 1), a.count - 1);
+            } else {
+#pragma unroll 8
+                for (size_t n = first + u; n < a.count; n += TPK) take(__ldg(x + n), n);
             }
-            if ((a.count & 1) && u == 0) take(__ldg(x + a.count - 1), a.count - 1);
-        } else {
-#pragma unroll 8
-            for (size_t n = u; n < a.count; n += TPK) take(__ldg(x + n), n);
+        };
+        // Fast form, whole windows of an aligned packet: for finite data the two comparisons are a plain maximum
+        // (one 3-input FMNMX with |.| modifiers per sample), and the thread's down-chirp entries repeat every window
+        // (its sample positions are congruent mod N), so they live in registers.  Whether the data IS finite is
+        // tracked by one packed FMA per sample (0*v + acc turns NaN as soon as any examined component is NaN or
+        // Inf); in that case the packet is rescanned in the exact form, so the result never differs.
+        constexpr int PER = N / (2 * TPK); // 16-byte pairs per thread per window
+        bool poisoned = false;
+        size_t done = 0;
+        if (aligned && PER >= 1) {
+            const ulonglong2* x2 = reinterpret_cast<const ulonglong2*>(x);
+            const size_t n_win = a.count / N;
+            c64 nan_acc = pk(0.0f, 0.0f);
+            const c64 zero2 = pk(0.0f, 0.0f);
+            auto windows = [&](auto dech) {
+                ulonglong2 dn[PER > 0 ? PER : 1];
+                if (dech.value) {
+#pragma unroll
+                    for (int k = 0; k < PER; ++k) dn[k] = __ldg(reinterpret_cast<const ulonglong2*>(a.down) + u + k * TPK);
+                }
+                auto one_sample = [&](c64 v, c64 d) {
+                    if (dech.value) v = cmul<true>(v, d, a.one);
+                    nan_acc = fma2(v, zero2, nan_acc);
+                    const float2 f = up(v);
+                    mx = fmaxf(mx, fmaxf(fabsf(f.x), fabsf(f.y)));
+                };
+                for (size_t w = 0; w < n_win; ++w) {
+                    const ulonglong2* xw = x2 + w * (size_t)(N / 2) + u;
+                    ulonglong2 v[PER > 0 ? PER : 1];
+#pragma unroll
+                    for (int k = 0; k < PER; ++k) v[k] = __ldg(xw + k * TPK);
+#pragma unroll
+                    for (int k = 0; k < PER; ++k) {
+                        one_sample(v[k].x, dn[k].x);
+                        one_sample(v[k].y, dn[k].y);
+                    }
+                }
+            };
+            if (a.dechirp) windows(std::true_type{});
+            else windows(std::false_type{});
+            done = n_win * (size_t)N;
+            const float2 na = up(nan_acc);
+            poisoned = na.x != na.x || na.y != na.y;
         }
+        scan_exact(done); // the samples after the last whole window (or everything, for an unaligned packet)
+        auto reduce = [&] {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { const float y = __shfl_xor_sync(0xffffffffu, mx, o); if (y > mx) mx = y; }
-        if (TPK > 32) {
-            if ((u & 31) == 0) redf[slot * (TPK / 32) + (u >> 5)] = mx;
-            Group<TPK>::sync(slot);
-            mx = redf[slot * (TPK / 32)];
+            for (int o = 16; o > 0; o >>= 1) { const float y = __shfl_xor_sync(0xffffffffu, mx, o); if (y > mx) mx = y; }
+            bool any = __any_sync(0xffffffffu, poisoned);
+            if (TPK > 32) {
+                if ((u & 31) == 0) { redf[slot * (TPK / 32) + (u >> 5)] = mx; redp[slot * (TPK / 32) + (u >> 5)] = any ? 1 : 0; }
+                Group<TPK>::sync(slot);
+                mx = redf[slot * (TPK / 32)];
+                any = redp[slot * (TPK / 32)] != 0;
 #pragma unroll
-            for (int w = 1; w < TPK / 32; ++w) if (redf[slot * (TPK / 32) + w] > mx) mx = redf[slot * (TPK / 32) + w];
+                for (int w = 1; w < TPK / 32; ++w) {
+                    if (redf[slot * (TPK / 32) + w] > mx) mx = redf[slot * (TPK / 32) + w];
+                    any = any || redp[slot * (TPK / 32) + w] != 0;
+                }
+                Group<TPK>::sync(slot); // redf/redp may be written again by the rescan
+            }
+            return any;
+        };
+        if (reduce()) { // NaN or Inf somewhere in the packet: the reference's comparison order matters
+            mx = 0.0f;
+            poisoned = false;
+            scan_exact(0);
+            reduce();
         }
         e.w = mx;
         e.z = (mx > 1.0f) ? __fdiv_rn(1.0f, mx) : 1.0f;

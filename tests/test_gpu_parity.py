@@ -161,6 +161,39 @@ def test_legacy_edge_cases(env):
     assert bits(co) == bits(eo[0]) and bits(to) == bits(eo[1])
 
 
+@pytest.mark.parametrize("sf", [7, 9, 12])
+def test_normalisation_scan_nan_inf(env, sf):
+    """LoRaDemod.cpp:59-77 compares, it does not call fmax: a NaN real part drops the whole sample, a NaN imaginary
+    part only itself.  The kernel's fast scan assumes finite data and must fall back to the exact order otherwise."""
+    L, ORC = env["L"], env["ORC"]
+    ctx = L.Context(sf)
+    n = 1 << sf
+    rng = np.random.default_rng(sf)
+    base = ((rng.standard_normal(6 * n + 37) + 1j * rng.standard_normal(6 * n + 37)) * 2).astype(np.complex64)
+
+    def expect(y):
+        mx = np.float32(0)
+        for v in y:  # the reference's loop, literally
+            a, b = np.abs(np.float32(v.real)), np.abs(np.float32(v.imag))
+            m = b if a < b else a
+            if m > mx:
+                mx = m
+        return mx
+
+    cases = []
+    y = base.copy(); y[3 * n + 5] = complex(np.nan, 50.0); cases.append(y)       # dropped: 50 must not win
+    y = base.copy(); y[4 * n + 9] = complex(40.0, np.nan); cases.append(y)       # 40 wins
+    y = base.copy(); y[2 * n + 1] = complex(np.nan, 50.0); y[5 * n + 2] = complex(-60.0, 1.0); cases.append(y)
+    y = base.copy(); y[6 * n + 30] = complex(np.nan, 70.0); cases.append(y)      # in the ragged tail
+    y = base.copy(); y[3 * n] = complex(1.0, -np.inf); cases.append(y)           # Inf wins, scale = 0
+    for y in cases + [base]:
+        ret, sym, sync, m = ctx.lora_demodulate(y)
+        want = expect(y)
+        assert bits(np.float32(m["max_amp"])) == bits(np.float32(want)), (sf, m["max_amp"], want)
+        ro, so, sy, mo = ORC.lora_demodulate(sf, y)
+        assert ret == ro
+
+
 def test_time_offset_shifts_both_directions(env):
     L, ORC, Params = env["L"], env["ORC"], env["Params"]
     ctx = L.Context(7, osr=2)
