@@ -329,9 +329,26 @@ def main():
     pk, pk_src = peaks()
     samples_step = wl.samples * world
     value = samples_step * args.steps / (ms_total * 1e-3) / 1e6
-    # roofline of the dominant kernel: 8*N*osr + 6 algorithmic bytes per window
+    # Roofline.  Algorithmic bytes: 8*N*osr + 6 per window.  The dominant kernel is the demod
+    # kernel of the largest SF (half of all samples of the sweep); `achieved` = its algorithmic bytes per launch over
+    # its average launch duration (CUDA events recorded by the library around the launch, on the launching stream).
     alg_bytes = sum(i["windows"] * (8 * (1 << i["sf"]) + 6) for i in wl.items) * args.steps
-    achieved = alg_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    achieved_all = alg_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    dom = max(wl.items, key=lambda i: per_sf[i["sf"]][0])
+    dom_ms, dom_k = per_sf[dom["sf"]]
+    dom_bytes = dom["windows"] * (8 * (1 << dom["sf"]) + 6)
+    achieved = dom_bytes / (dom_ms / max(dom_k, 1) * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    # DRAM traffic of that kernel from the committed ncu --set full capture (bytes moved per algorithmic byte),
+    # scaled to this launch's size; null when no capture of this SF's kernel is on file.
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            tj = json.load(f)
+        if int(tj["sf"]) == dom["sf"]:
+            traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"] * dom_bytes
+            traffic_src = tj["source"]
+    except (OSError, KeyError, ValueError):
+        pass
     per_sf_out = {}
     for i in wl.items:
         ms_sf, k_sf = per_sf[i["sf"]]
@@ -394,9 +411,13 @@ def main():
                    "per_sf": per_sf_out},
         "clocks": clock_info, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_src,
-                     "kernel": "demod_kernel<SF> (fused dechirp + rotate + FFT + argmax)",
-                     "kernel_ms_per_step": k_ms / args.steps, "kernel_launches": k_n},
+                     "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_source": pk_src,
+                     "kernel": f"demod_blocked_kernel<SF={dom['sf']}, fused flavour> (dechirp + rotate + FFT + argmax), "
+                               "timed with its margin-recheck launch",
+                     "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms_per_launch": dom_ms / max(dom_k, 1),
+                     "traffic_source": traffic_src,
+                     "all_sf": {"achieved": achieved_all, "frac": achieved_all / pk["hbm_gbs"],
+                                "kernel_ms_per_step": k_ms / args.steps, "kernel_launches": k_n}},
     }
     if e2e:
         line["e2e"] = e2e
