@@ -120,7 +120,7 @@ size_t orc_stream_demod(unsigned sf, unsigned char sync, float thresh, size_t mt
     int state = FRAMESYNC;                 /* activate(), :138-142 */
     const orc_c32* chirp = up;
     int fine_idx = 0, freq_err = 0;
-    float fine_err = 0.0f;                 /* members are zero-initialised by the constructor's init list */
+    float fine_err = 0.0f;                 /* _finefreqError: see the note on prev_value */
     short prev_value = 0;                  /* _prevValue, _freqError, _finefreqError are left uninitialised by the
                                               reference's constructor (:68-75); zero is assumed here */
     size_t sym_count = 0, n_pkt = 0, sym_used = 0, pos = 0;
