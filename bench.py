@@ -321,6 +321,39 @@ def main():
         crc_ok[i["sf"]] = round(float((r["crc_ok"] == 1).mean()), 4)
         sym_ok[i["sf"]] = round(float((i["rx"] == i["tx"]).float().mean().item()), 4)
 
+    # e2e: the same metric through the host-buffer C-ABI call (lora_b200_receive_host), pinned HOST buffers in,
+    # payloads / results / metrics out, H2D and D2H copies inside the timed region; every rank does its own share,
+    # the time is the max over ranks.
+    pe = min(args.e2e_packets, packets)
+    pinned = []
+    for i in wl.items:
+        h = torch.empty((pe, i["iq"].shape[1]), dtype=torch.complex64, pin_memory=True)
+        h.copy_(i["iq"][:pe])
+        pinned.append((i, h.numpy(), np.zeros((pe, L.PAYLOAD_STRIDE), np.uint8), np.zeros(pe, L.CHAIN_RESULT),
+                       np.zeros(pe, L.PKT_METRICS), h))
+    torch.cuda.synchronize()
+
+    def e2e_step():
+        for i, h_iq, pay, res, met, _ in pinned:
+            i["ctx"].receive_host(i["cfg"], h_iq, mode=mode, payload=pay, results=res, metrics=met)
+
+    for _ in range(2):
+        e2e_step()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    dt_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(dt_t, op=dist.ReduceOp.MAX)
+    dt = float(dt_t.item())
+    e_samples = sum(h.size for _, h, _, _, _, _ in pinned)
+    e2e = {"value": e_samples * world * args.steps / dt / 1e6, "unit": "Msamples/s",
+           "h2d_bytes_per_step": int(e_samples * 8) * world,
+           "d2h_bytes_per_step": int(sum(p.nbytes + r.nbytes + m.nbytes for _, _, p, r, m, _ in pinned)) * world,
+           "sample": f"{pe} packets per SF per GPU through lora_b200_receive_host, pinned host buffers"}
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -358,34 +391,9 @@ def main():
                                     "Msamples_s": round(i["samples"] * max(k_sf, 1) / (ms_sf * 1e-3) / 1e6, 1) if ms_sf > 0 else 0.0,
                                     "crc_ok": crc_ok[i["sf"]], "symbols_eq_tx": sym_ok[i["sf"]]}
 
-    # e2e: the same metric through the host-buffer C-ABI call, copies inside the timed region
-    e2e = None
+    # cpu_baseline: the same packets as the e2e sample, the reference's CPU path on this box's host cores
     cpu = None
     if world == 1:
-        pe = min(args.e2e_packets, packets)
-        pinned = []
-        for i in wl.items:
-            h = torch.empty((pe, i["iq"].shape[1]), dtype=torch.complex64, pin_memory=True)
-            h.copy_(i["iq"][:pe])
-            pinned.append((i, h.numpy(), np.zeros((pe, L.PAYLOAD_STRIDE), np.uint8), np.zeros(pe, L.CHAIN_RESULT),
-                           np.zeros(pe, L.PKT_METRICS), h))
-        torch.cuda.synchronize()
-
-        def e2e_step():
-            for i, h_iq, pay, res, met, _ in pinned:
-                i["ctx"].receive_host(i["cfg"], h_iq, mode=mode, payload=pay, results=res, metrics=met)
-
-        for _ in range(2):
-            e2e_step()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            e2e_step()
-        dt = time.perf_counter() - t0
-        e_samples = sum(h.size for _, h, _, _, _, _ in pinned)
-        e2e = {"value": e_samples * args.steps / dt / 1e6, "unit": "Msamples/s",
-               "h2d_bytes_per_step": int(e_samples * 8),
-               "d2h_bytes_per_step": int(sum(p.nbytes + r.nbytes + m.nbytes for _, _, p, r, m, _ in pinned)),
-               "sample": f"{pe} packets per SF through lora_b200_receive_host, pinned host buffers"}
         # same packets, the reference's CPU path on this box's host cores
         pc = min(args.cpu_packets, pe)
         threads = os.cpu_count() or 1
