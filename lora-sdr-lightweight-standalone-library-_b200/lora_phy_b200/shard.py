@@ -37,3 +37,35 @@ def gather_records(local, dist, out=None):
         out = torch.empty((world * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(out, local.contiguous())
     return out
+
+
+def stream_segments(count, n_segments, n, mtu=256, preamble_symbols=16):
+    """Cut one long capture of `count` samples into `n_segments` pieces for the frame synchroniser (SURVEY.md 8e,
+    "overlap-save by one maximum frame").  Segment k OWNS [own_lo, own_hi) -- a partition of [0, count) -- and READS
+    [lo, hi): `preamble_symbols*n` samples earlier, so a frame whose data starts just inside the owned range still has
+    its whole preamble (10 up-chirps, sync word, 2 1/4 down-chirps) in view, and `(mtu + 2)*n` samples later, so a
+    packet that starts at the end of the owned range is seen to its last symbol.  -> list of dicts."""
+    if n_segments < 1 or count < 0:
+        raise ValueError("bad segmentation")
+    out = []
+    for k in range(n_segments):
+        own_lo = count * k // n_segments
+        own_hi = count * (k + 1) // n_segments
+        lo = max(0, own_lo - preamble_symbols * n)
+        hi = min(count, own_hi + (mtu + 2) * n)
+        out.append({"own_lo": own_lo, "own_hi": own_hi, "lo": lo, "hi": hi})
+    return out
+
+
+def merge_stream_packets(segments, per_segment):
+    """per_segment[k] = [(start_in_segment, symbols, freq_error), ...] as the synchroniser reported them for the
+    samples [lo, hi) of segment k.  A packet is kept from the segment that owns its first data sample, which removes
+    the copies neighbouring segments see in their overlap.  -> [(absolute_start, symbols, freq_error)] in stream order."""
+    merged = []
+    for seg, packets in zip(segments, per_segment):
+        for start, symbols, err in packets:
+            at = seg["lo"] + int(start)
+            if seg["own_lo"] <= at < seg["own_hi"]:
+                merged.append((at, symbols, err))
+    merged.sort(key=lambda p: p[0])
+    return merged
