@@ -20,13 +20,13 @@ namespace {
 
 // ---- the fine-tune index walk ---------------------------------------------------------------------------------
 // LoRaDemod.cpp:157-165: per sample, an int index is converted to float, reduced by fine_err*128 (a float), truncated
-// back to int and wrapped once.  The rounding of the float subtraction depends on the binade of the index, so the
-// walk is piecewise arithmetic: constant stride inside a binade, with breaks at binade crossings, wraps and ties.
-// It is evaluated exactly without serialising it: guess an arithmetic progression from a known-correct start, let
-// every thread check "one exact step from my guessed index gives the next guessed index" for its own positions,
-// and accept the prefix before the first failed check (induction over positions).  The step after that prefix is
+// back to int and wrapped once.  The rounding of the float subtraction depends on the binade of the difference, so
+// the walk is piecewise regular: a closed form (see fine_walk) with breaks at binade crossings and ties.
+// It is evaluated exactly without serialising it: guess the closed form from a known-correct start, let every
+// thread check "one exact step from my guessed index gives the next guessed index" for its own positions, and
+// accept the prefix before the first failed check (induction over positions).  The step after that prefix is
 // recomputed exactly and becomes the next start.  A round costs 16 exact steps per thread and one group minimum;
-// the number of rounds is the number of breaks (typically 1-3 per window).
+// the number of rounds is the number of breaks (usually one round per window).
 template <int N>
 PM_DEV int fine_step(int idx, float d)
 {
@@ -65,7 +65,8 @@ template <int SF>
 PM_DEV void fine_walk(int idx0, float fine_err, int t, int slot, int* scratch, int (&idx)[16], int& carry)
 {
     using B = Blk<SF>;
-    constexpr int N = B::N, T = B::T, W = N * STREAM_FINE_STEPS;
+    constexpr int N = B::N, T = B::T;
+    constexpr unsigned W = N * STREAM_FINE_STEPS;
     const float d = __fmul_rn(fine_err, (float)STREAM_FINE_STEPS);
     if (d == 0.0f) { // (int)((float)idx - 0) == idx
 #pragma unroll
@@ -73,32 +74,44 @@ PM_DEV void fine_walk(int idx0, float fine_err, int t, int slot, int* scratch, i
         carry = idx0;
         return;
     }
+    // The walk is an arithmetic progression modulo W while the float difference stays non-negative (truncation =
+    // floor).  For a positive fractional d the difference goes negative just before every wrap, truncation toward
+    // zero then takes one unit less, and the wrap adds W: together that is the SAME stride modulo W + 1.  (The one
+    // exception, an index equal to floor(d), and the rare d whose fraction is below the float grid of the
+    // difference are caught by the check below like any other break.)
+    const unsigned Mod = (d > 0.0f && d != truncf(d)) ? W + 1u : W;
     int base_pos = 0, base_idx = idx0;
     for (int round = 0;; ++round) {
-        const unsigned s = (unsigned)(base_idx - fine_step<N>(base_idx, d)); // guessed stride, modulo 2^32 (W | 2^32)
+        const int diff = base_idx - fine_step<N>(base_idx, d);                // in (-W, W)
+        const unsigned s = diff < 0 ? (unsigned)(diff + (int)Mod) : (unsigned)diff; // guessed stride in [0, Mod)
+        const unsigned step_t = ((unsigned)T * s) % Mod;                          // T*s < 2^8 * 2^20: 32-bit arithmetic throughout
+        const int j0 = base_pos <= t ? 0 : (base_pos - t + T - 1) / T;        // first of this thread's positions >= base_pos
+        const unsigned k0 = (unsigned)(t + T * j0 - base_pos);                // < T
+        unsigned h = ((unsigned)base_idx + Mod - (k0 * s) % Mod) % Mod;
         int fail = N;
         int guess[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            const int p = t + T * j;
-            const unsigned k = (unsigned)(p - base_pos);
-            const int h = (int)(((unsigned)base_idx - k * s) & (unsigned)(W - 1));
-            const int hn = (int)(((unsigned)h - s) & (unsigned)(W - 1));
-            guess[j] = h;
-            if (p >= base_pos && fine_step<N>(h, d) != hn) fail = min(fail, p);
+            if (j >= j0) {
+                const unsigned hn = h >= s ? h - s : h + Mod - s;
+                guess[j] = (int)h;
+                if ((unsigned)fine_step<N>((int)h, d) != hn) fail = min(fail, t + T * j);
+                h = h >= step_t ? h - step_t : h + Mod - step_t;
+            }
         }
         const int pf = group_min<T>(fail, t, slot, scratch, round); // first position whose successor is not the guess
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             const int p = t + T * j;
-            if (p >= base_pos && p <= pf) idx[j] = guess[j];
+            if (j >= j0 && p <= pf) idx[j] = guess[j];
         }
+        const unsigned span = (unsigned)((pf >= N ? N : pf) - base_pos);      // steps from the base to the last accepted guess
+        const unsigned h_last = ((unsigned)base_idx + Mod - (span * s) % Mod) % Mod; // span*s <= 2^12 * 2^19 + 2^12 < 2^32
         if (pf >= N) { // every check passed, including the one at N-1 that validates position N
-            carry = (int)(((unsigned)base_idx - (unsigned)(N - base_pos) * s) & (unsigned)(W - 1));
+            carry = (int)h_last;
             return;
         }
-        const int h_pf = (int)(((unsigned)base_idx - (unsigned)(pf - base_pos) * s) & (unsigned)(W - 1));
-        base_idx = fine_step<N>(h_pf, d);
+        base_idx = fine_step<N>((int)h_last, d); // exact successor of the last accepted position
         base_pos = pf + 1;
         if (base_pos >= N) { carry = base_idx; return; }
     }
