@@ -21,9 +21,12 @@ def main():
     ap.add_argument("--precision", default="fast", choices=["fast", "exact"])
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace", "legacy"])
+    ap.add_argument("--lib", default=None, help="variant library built by scripts/ab_build.sh (same-box A/B timing)")
     args = ap.parse_args()
     import torch
     import lora_phy_b200 as L
+    if args.lib:
+        L.LIB_PATH = os.path.abspath(args.lib)
 
     sf = args.sf
     ctx = L.Context(sf)

@@ -335,3 +335,36 @@ def test_compensate_encode_decode_host_entry_points(env):
     out, ok = ctx.decode(sym)
     o_out, o_ok = ORC.decode(sym)
     assert bits(out) == bits(o_out) and ok == bool(o_ok)
+
+
+@pytest.mark.parametrize("sf", [7, 9, 10, 11, 12])
+def test_repeatable_under_load(env, sf):
+    """The kernels reuse one shared-memory exchange region window after window behind hand-placed barriers (the
+    end-of-window barrier is gone: the peak search is the rendezvous).  compute-sanitizer is not available on the
+    GPU pool, so a missing barrier has to show up as what it would cause: results that change from run to run, or
+    differ between a loaded GPU (all CTAs resident, every slot busy) and the oracle."""
+    torch, L, ORC = env["torch"], env["L"], env["ORC"]
+    ctx = L.Context(sf)
+    n_pk, nsym = (8192 >> max(0, sf - 8)), 10
+    gen = torch.Generator(device="cuda").manual_seed(7 * sf)
+    tx = torch.randint(0, 1 << sf, (n_pk, nsym), dtype=torch.int16, device="cuda", generator=gen)
+    iq = ctx.modulate_batch(tx)
+    snr = torch.full((n_pk,), -14.0, dtype=torch.float32, device="cuda")   # near-ties are common at this SNR
+    ctx.awgn_batch(iq, snr, seed=sf)
+    down = ORC.gen_chirp(1 << sf, 1, 1 << sf, 0.0, True, 1.0, 0.0, 1.0)[0]
+    for precision in (L.PRECISION_FAST, L.PRECISION_EXACT):
+        ctx.set_precision(precision)
+        first = None
+        for rep in range(12):
+            rx, met, pk = ctx.demod_batch(iq, mode=L.DEMOD_LEGACY_DECHIRP, want_peaks=True)
+            cur = (rx.clone(), met.clone(), pk.clone())
+            if first is None:
+                first = cur
+            else:
+                for a, b in zip(first, cur):
+                    assert torch.equal(a.view(torch.uint8), b.view(torch.uint8)), (sf, precision, rep)
+        rx_h = first[0].cpu().numpy().view(np.uint16)
+        h_iq = iq[:: max(1, n_pk // 24)].cpu().numpy()
+        for k, p in enumerate(range(0, n_pk, max(1, n_pk // 24))):
+            _, so, _, _ = ORC.lora_demodulate(sf, unfused_dechirp(h_iq[k], down))
+            assert bits(rx_h[p]) == bits(so), (sf, precision, p)

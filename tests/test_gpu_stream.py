@@ -148,3 +148,37 @@ def test_stream_detect_edge_cases(env):
     # osr != 1 is refused loudly
     with pytest.raises(L.LoraB200Error):
         L.Context(sf, osr=2).stream_detect_batch(torch.from_numpy(x[None]).cuda())
+
+
+def test_stream_detect_repeatable_under_load(env):
+    """Same purpose as test_repeatable_under_load in test_gpu_parity.py, for the stream kernel: every slot busy, many
+    rounds of the index walk (which synchronises through shared memory), identical results run after run."""
+    torch, L, ORC = env["torch"], env["L"], env["ORC"]
+    sf, n = 10, 1024
+    rng = np.random.default_rng(17)
+    frames = []
+    for i in range(8):
+        sym = rng.integers(0, n, 14, dtype=np.uint16)
+        frames.append(channel(ORC.frame_modulate(sf, sym, padding=2, ampl=1.0), n, 2 * n + int(rng.integers(0, n)), n,
+                              float(rng.uniform(-200, 200)), 12.0, rng, ampl=1.0))
+    size = max(len(f) for f in frames)
+    base = np.stack([np.concatenate([f, np.zeros(size - len(f), np.complex64)]) for f in frames])
+    x = torch.from_numpy(np.tile(base, (160, 1))).cuda()          # 1280 streams: more than one wave of slots
+    ctx = L.Context(sf)
+    first = None
+    for rep in range(6):
+        sym, pk, res = ctx.stream_detect_batch(x, mtu=14, thresh_db=-8.0)
+        cur = (sym.clone(), pk.clone(), res.clone())
+        if first is None:
+            first = cur
+        else:
+            for a, b in zip(first, cur):
+                assert torch.equal(a, b), rep
+    sym, pk, res = first
+    for k in range(8):                                             # every copy of a stream gives the same answer
+        for a in (sym, pk, res):
+            blk = a[k::8]
+            assert (blk == blk[0]).all()
+    want, start, err, consumed = ORC.stream_demod(sf, base[3], mtu=14, thresh=-8.0)
+    pk_h, res_h = L.stream_records(pk, res)
+    assert int(res_h[3]["n_packets"]) == len(want) and int(res_h[3]["consumed"]) == consumed
