@@ -157,3 +157,30 @@ def test_config3_mixed_sf_streams_match_oracle(env):
                         found_exact += int(np.all(d_sym == d_sym[0]))
                         break
     assert sent > 40 and found_exact >= 0.8 * sent, (sent, found_exact)
+
+
+def test_golden_capture_frame_train_is_found(env):
+    """SURVEY 8(f) rank 1, first step: the committed SF7 capture is a 2x oversampled train of standard frames that
+    demodulate() only cuts into aligned windows.  Decimated by two, the frame synchroniser locks onto every complete
+    frame (15, one every 65.25 symbols = 8 preamble + 2 sync + 2.25 down-chirps + 53 data) and the header block of
+    each decodes to a consistent length -- identically on the GPU and in the oracle."""
+    import os
+    torch, L, ORC = env["torch"], env["L"], env["ORC"]
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "capture_sf7.npz"))
+    x = np.ascontiguousarray(g["iq"][1::2])
+    ctx = L.Context(7)
+    sym, pk, res = ctx.stream_detect_batch(torch.from_numpy(x[None]).cuda(), mtu=53, max_packets=32, max_symbols=2048)
+    pk, res = L.stream_records(pk, res)
+    want, start, err, consumed = ORC.stream_demod(7, x, mtu=53, pkt_cap=32)
+    assert int(res[0]["n_packets"]) == len(want) == 15 and int(res[0]["consumed"]) == consumed
+    assert [int(p["start"]) for p in pk[0, :15]] == [int(s) for s in start] == [1568 + 8352 * k for k in range(15)]
+    sym = sym.cpu().numpy()[0]
+    cfg = L.chain_cfg(7, 1)
+    d_sym = torch.from_numpy(sym[: 15 * 53].reshape(15, 53).copy()).cuda()
+    out, r = ctx.chain_decode_batch(cfg, d_sym)
+    r = r.cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)
+    for k in range(15):
+        assert bits(sym[53 * k: 53 * (k + 1)]) == bits(want[k])
+        _, _, info = ORC.chain_decode(env["orc_chain_cfg"](7, 1), want[k].astype(np.uint16))
+        assert int(r[k]["hdr_length"]) == info.hdr_length and int(r[k]["hdr_length"]) in (30, 31)
+        assert int(r[k]["hdr_has_crc"]) == info.hdr_has_crc and int(r[k]["hdr_rdd"]) == info.hdr_rdd
