@@ -202,6 +202,15 @@ int lora_b200_receive_host(lora_b200_ctx* ctx, int mode, const lora_b200_chain_c
                            const lora_b200_c32* h_iq, size_t n_packets, size_t samples_per_packet,
                            uint8_t* h_payload, lora_b200_chain_result* h_results,
                            lora_b200_pkt_metrics* h_metrics);
+/* The same call for SDR sample formats: interleaved int16 I,Q as most front ends
+ * deliver them, 4 bytes per sample over PCIe instead of 8.  Samples are converted on the device to
+ * float32 * scale (exact for scale = 2^-15) and then take exactly the path of lora_b200_receive_host, so the results
+ * equal those of the float call on the converted samples.  The runners' float32 file format
+ * (runners/rx_runner.cpp:74-79) is unchanged. */
+int lora_b200_receive_host_i16(lora_b200_ctx* ctx, int mode, const lora_b200_chain_cfg* cfg,
+                               const int16_t* h_iq, size_t n_packets, size_t samples_per_packet, float scale,
+                               uint8_t* h_payload, lora_b200_chain_result* h_results,
+                               lora_b200_pkt_metrics* h_metrics);
 
 /* ---- continuous-stream front end and full frames (upstream Pothos blocks) --------------------------------------
  * LoRaDemod::work (LoRa-SDR/LoRaDemod.cpp:145-327): the frame synchroniser state machine -- 10-chirp preamble with

@@ -84,7 +84,7 @@ struct lora_b200_ctx {
     uint8_t* d_whiten = nullptr; // 2 x WHITEN_LEN bytes
     float2* d_stream_tables = nullptr; // up (N), down (N), fine (128 N): built by the first stream_detect call
     Buf est, sync_raw;           // per-packet scratch of the demod kernels
-    Buf s_iq, s_sym, s_metrics, s_payload, s_results, s_misc; // staging for the host-buffer entry points
+    Buf s_iq, s_sym, s_metrics, s_payload, s_results, s_misc, s_raw; // staging for the host-buffer entry points
     Buf h_pin;                   // pinned bounce buffer
     cudaStream_t stream = nullptr;
     // prepass / demod pipeline of large batches: the scan+estimate of sub-batch k+1 runs beside the demod of k
@@ -183,7 +183,7 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
     cudaFree(c->d_stat_rechecked);
     cudaFree(c->d_stream_tables);
     for (Buf* b : {&c->flags, &c->est, &c->sync_raw, &c->s_iq, &c->s_sym, &c->s_metrics, &c->s_payload, &c->s_results,
-                   &c->s_misc, &c->h_pin})
+                   &c->s_misc, &c->s_raw, &c->h_pin})
         b->release();
     for (auto& pr : c->ev_pool) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -738,27 +738,18 @@ extern "C" int lora_b200_modulate_host(lora_b200_ctx* c, const uint16_t* h_symbo
     return LORA_B200_OK;
 }
 
-extern "C" int lora_b200_receive_host(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
-                                      const lora_b200_c32* h_iq, size_t n_packets, size_t count,
-                                      uint8_t* h_payload, lora_b200_chain_result* h_results,
-                                      lora_b200_pkt_metrics* h_metrics)
+// demod + chain decode of device-resident IQ, results copied to host buffers; st is synchronised before returning
+static int receive_device_locked(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g, const float2* d_iq,
+                                 size_t n_packets, size_t count, uint8_t* h_payload, lora_b200_chain_result* h_results,
+                                 lora_b200_pkt_metrics* h_metrics, cudaStream_t st)
 {
-    if (!c || !h_iq || !h_payload || !h_results) return fail(LORA_B200_EINVAL, "null argument");
-    if (n_packets == 0) return LORA_B200_OK;
-    std::lock_guard<std::mutex> lk(c->mu);
-    CU(cudaSetDevice(c->device));
     const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
-    const size_t total = count / step;
-    if (total < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
-    const size_t nsym = total - 2;
-    CU(c->s_iq.reserve(sizeof(float2) * count * n_packets));
+    const size_t nsym = count / step - 2;
     CU(c->s_sym.reserve(sizeof(uint16_t) * nsym * n_packets + 2));
     CU(c->s_metrics.reserve(sizeof(lora_b200_pkt_metrics) * n_packets));
     CU(c->s_payload.reserve(static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * n_packets));
     CU(c->s_results.reserve(sizeof(lora_b200_chain_result) * n_packets));
-    cudaStream_t st = c->stream;
-    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count * n_packets, cudaMemcpyHostToDevice, st));
-    int rc = demod_batch_locked(c, mode, c->s_iq.as<float2>(), n_packets, count, count, c->s_sym.as<uint16_t>(), nsym,
+    int rc = demod_batch_locked(c, mode, d_iq, n_packets, count, count, c->s_sym.as<uint16_t>(), nsym,
                                 nullptr, c->s_metrics.as<lora_b200_pkt_metrics>(), st);
     if (rc) return rc;
     rc = chain_decode_locked(c, g, c->s_sym.as<uint16_t>(), n_packets, nsym, nsym, c->s_payload.as<uint8_t>(),
@@ -770,6 +761,41 @@ extern "C" int lora_b200_receive_host(lora_b200_ctx* c, int mode, const lora_b20
         CU(cudaMemcpyAsync(h_metrics, c->s_metrics.p, sizeof(lora_b200_pkt_metrics) * n_packets, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_receive_host(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
+                                      const lora_b200_c32* h_iq, size_t n_packets, size_t count,
+                                      uint8_t* h_payload, lora_b200_chain_result* h_results,
+                                      lora_b200_pkt_metrics* h_metrics)
+{
+    if (!c || !h_iq || !h_payload || !h_results) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_packets == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (count / (static_cast<size_t>(c->n) * c->cfg.osr) < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
+    CU(c->s_iq.reserve(sizeof(float2) * count * n_packets));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count * n_packets, cudaMemcpyHostToDevice, st));
+    return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
+}
+
+extern "C" int lora_b200_receive_host_i16(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
+                                          const int16_t* h_iq, size_t n_packets, size_t count, float scale,
+                                          uint8_t* h_payload, lora_b200_chain_result* h_results,
+                                          lora_b200_pkt_metrics* h_metrics)
+{
+    if (!c || !h_iq || !h_payload || !h_results) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_packets == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (count / (static_cast<size_t>(c->n) * c->cfg.osr) < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
+    const size_t samples = count * n_packets;
+    CU(c->s_iq.reserve(sizeof(float2) * samples));
+    CU(c->s_raw.reserve(sizeof(short2) * samples));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_raw.p, h_iq, sizeof(short2) * samples, cudaMemcpyHostToDevice, st));
+    CU(launch_convert_i16(c->s_raw.as<short2>(), c->s_iq.as<float2>(), samples, scale, c->sm_count, st));
+    return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
 }
 
 // ---- small host-buffer entry points used by include/lora_phy/phy.hpp -------------------------------------------

@@ -382,4 +382,38 @@ cudaError_t launch_finalize(const FinalizeArgs& a, cudaStream_t st)
     return cudaGetLastError();
 }
 
+__global__ void __launch_bounds__(256) convert_i16_kernel(const short2* __restrict__ in, float2* __restrict__ out, size_t n, float scale)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t n4 = ((reinterpret_cast<uintptr_t>(in) & 15u) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) ? n / 4 : 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) { // 4 samples: 16 bytes in, 32 out
+        const int4 v = __ldg(reinterpret_cast<const int4*>(in) + i);
+        const int w[4] = {v.x, v.y, v.z, v.w};
+        float4 o[2];
+        float* f = reinterpret_cast<float*>(o);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            f[2 * k] = __fmul_rn((float)(short)(w[k] & 0xffff), scale);
+            f[2 * k + 1] = __fmul_rn((float)(short)(w[k] >> 16), scale);
+        }
+        reinterpret_cast<float4*>(out)[2 * i] = o[0];
+        reinterpret_cast<float4*>(out)[2 * i + 1] = o[1];
+    }
+    for (size_t i = 4 * n4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const short2 v = in[i];
+        out[i] = make_float2(__fmul_rn((float)v.x, scale), __fmul_rn((float)v.y, scale));
+    }
+}
+
+cudaError_t launch_convert_i16(const short2* in, float2* out, size_t n, float scale, int sm_count, cudaStream_t st)
+{
+    size_t blocks = (n / 4 + 255) / 256;
+    const size_t cap = (size_t)sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    convert_i16_kernel<<<(unsigned)blocks, 256, 0, st>>>(in, out, n, scale);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
 } // namespace lora_b200

@@ -75,4 +75,7 @@ cudaError_t launch_fill_est(float4* est, int n_packets, cudaStream_t st);
 
 extern unsigned long long g_launches; // kernels launched by this library (bench.py's gpu_launches)
 
+// SDR sample ingest: interleaved int16 (I, Q) -> float32 * scale.  With scale = 2^-15 the conversion is exact.
+cudaError_t launch_convert_i16(const short2* in, float2* out, size_t n, float scale, int sm_count, cudaStream_t st);
+
 } // namespace lora_b200

@@ -368,3 +368,24 @@ def test_repeatable_under_load(env, sf):
         for k, p in enumerate(range(0, n_pk, max(1, n_pk // 24))):
             _, so, _, _ = ORC.lora_demodulate(sf, unfused_dechirp(h_iq[k], down))
             assert bits(rx_h[p]) == bits(so), (sf, precision, p)
+
+
+def test_int16_ingest_equals_float_path(env):
+    """int16 I/Q in, converted on the device (exactly, scale 2^-15), then the float path."""
+    torch, L = env["torch"], env["L"]
+    for sf in (7, 10):
+        ctx = L.Context(sf)
+        cfg = L.chain_cfg(sf, 1)
+        gen = torch.Generator(device="cuda").manual_seed(sf)
+        pay = torch.randint(0, 256, (33, 16), dtype=torch.uint8, device="cuda", generator=gen)
+        iq = ctx.modulate_batch(ctx.chain_encode_batch(cfg, pay), amplitude=0.25)
+        ctx.awgn_batch(iq, torch.full((33,), 20.0, device="cuda"), seed=sf)   # sigma is relative to amplitude 1
+        h = iq.cpu().numpy()
+        q = np.stack([h.real, h.imag], axis=-1)
+        q = np.clip(np.round(q * 8192.0), -32768, 32767).astype(np.int16)           # a 14-bit ADC's view of the samples
+        as_float = (q.astype(np.float32) * np.float32(1.0 / 32768.0))
+        as_float = (as_float[..., 0] + 1j * as_float[..., 1]).astype(np.complex64)
+        p1, r1, m1 = ctx.receive_host_i16(cfg, q)
+        p2, r2, m2 = ctx.receive_host(cfg, as_float)
+        assert bits(p1) == bits(p2) and bits(r1) == bits(r2) and bits(m1) == bits(m2)
+        assert (r1["crc_ok"] == 1).all() and bytes(p1[:, :16]) == bytes(pay.cpu().numpy())
