@@ -389,3 +389,24 @@ def test_int16_ingest_equals_float_path(env):
         p2, r2, m2 = ctx.receive_host(cfg, as_float)
         assert bits(p1) == bits(p2) and bits(r1) == bits(r2) and bits(m1) == bits(m2)
         assert (r1["crc_ok"] == 1).all() and bytes(p1[:, :16]) == bytes(pay.cpu().numpy())
+
+
+def test_stream_pipelined_sub_batches_give_the_same_results(env):
+    """lora_b200_set_overlap: scan+estimate of sub-batch k+1 on a second stream beside the demod of sub-batch k (only
+    taken for batches of 256 MB and more).  Off by default because it is no faster; it must still be exact."""
+    torch, L = env["torch"], env["L"]
+    sf = 9
+    ctx = L.Context(sf)
+    gen = torch.Generator(device="cuda").manual_seed(99)
+    tx = torch.randint(0, 1 << sf, (4608, 28), dtype=torch.int16, device="cuda", generator=gen)
+    iq = ctx.modulate_batch(tx)
+    assert iq.numel() * 8 >= 256 << 20
+    ctx.awgn_batch(iq, torch.full((4608,), -12.0, device="cuda"), seed=5)
+    out = []
+    for on in (False, True):
+        ctx.set_overlap(on)
+        rx, met, pk = ctx.demod_batch(iq, mode=L.DEMOD_LEGACY_DECHIRP, want_peaks=True)
+        torch.cuda.synchronize()
+        out.append((rx.clone(), met.clone(), pk.clone()))
+    for a, b in zip(*out):
+        assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
