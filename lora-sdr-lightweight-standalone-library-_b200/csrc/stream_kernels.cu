@@ -80,6 +80,35 @@ PM_DEV void fine_walk(int idx0, float fine_err, int t, int slot, int* scratch, i
     // exception, an index equal to floor(d), and the rare d whose fraction is below the float grid of the
     // difference are caught by the check below like any other break.)
     const unsigned Mod = (d > 0.0f && d != truncf(d)) ? W + 1u : W;
+    // Shortcut, taken by ~7 windows in 8: when |d| < W and its fraction is either zero or at least 1/16 away from
+    // an integer, the float subtraction (whose result is below 2^20, so rounded to a grid of 1/16 or finer) can
+    // never round across an integer, truncation gives exactly what real arithmetic would, and the closed form needs
+    // no checking -- except that modulo W + 1 it produces W where the true walk, passing through floor(d), goes to
+    // 0.  A guess equal to W at any position sends the window to the checked path below.
+    {
+        const float ad = fabsf(d), fl = floorf(ad), fr = ad - fl;
+        if (ad < (float)W && (fr == 0.0f || (fr >= 0.0625f && fr <= 0.9375f))) {
+            const unsigned whole = (unsigned)fl;
+            // stride subtracted per step, modulo Mod: d > 0 -> floor(d) (+1 if fractional); d < 0 -> adding floor(|d|)
+            const unsigned s = d > 0.0f ? whole + (fr != 0.0f ? 1u : 0u) : (whole == 0u ? 0u : Mod - whole);
+            const unsigned step_t = ((unsigned)T * s) % Mod;
+            unsigned h = ((unsigned)idx0 + Mod - ((unsigned)t * s) % Mod) % Mod;
+            bool hit_w = false;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                idx[j] = (int)h;
+                hit_w = hit_w || h == W;
+                h = h >= step_t ? h - step_t : h + Mod - step_t;
+            }
+            const unsigned last = ((unsigned)idx0 + Mod - ((unsigned)N * s) % Mod) % Mod; // position N: N*s < 2^32
+            hit_w = hit_w || last == W;
+            if (group_min<T>(hit_w ? 0 : 1, t, slot, scratch, 0) != 0) {
+                carry = (int)last;
+                return;
+            }
+            Group<T>::sync(slot); // the scratch buffer of round 0 is written again below
+        }
+    }
     int base_pos = 0, base_idx = idx0;
     for (int round = 0;; ++round) {
         const int diff = base_idx - fine_step<N>(base_idx, d);                // in (-W, W)
