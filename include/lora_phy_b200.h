@@ -216,7 +216,9 @@ int lora_b200_receive_host_i16(lora_b200_ctx* ctx, int mode, const lora_b200_cha
  * LoRaDemod::work (LoRa-SDR/LoRaDemod.cpp:145-327): the frame synchroniser state machine -- 10-chirp preamble with
  * fractional-bin fine tuning, two sync-word chirps, two down-chirps for the frequency error, the quarter chirp, then
  * data symbols until `mtu` symbols or a squelched window -- run over n_streams independent sample streams (gateway
- * channels, or segments of a long capture), one stream per group of N/16 threads.  osr must be 1 and sf 7..12.
+ * channels, or segments of a long capture), one stream per group of N/16 threads.  sf 7..12.  With osr > 1 the
+ * stream is decimated on the fly (samples 0, osr, 2*osr, ... -- the indexing of phy.cpp:216); positions and
+ * `consumed` are then counted in decimated samples.
  * LoRaMod::work (LoRa-SDR/LoRaMod.cpp:109-238): the frame generator that produces such streams. */
 typedef struct lora_b200_stream_cfg {
     uint8_t sync;          /* LoRaDemod::setSync, default 0x12 */

@@ -907,8 +907,8 @@ extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_s
     if (!c || !cfg || !d_results) return fail(LORA_B200_EINVAL, "null argument");
     if (n_streams == 0) return LORA_B200_OK;
     if (!d_iq || (!d_symbols && cfg->max_symbols) || (!d_packets && cfg->max_packets)) return fail(LORA_B200_EINVAL, "null argument");
-    if (c->cfg.osr != 1 || !blocked_supported(static_cast<int>(c->cfg.sf)))
-        return fail(LORA_B200_EINVAL, "stream detection needs osr 1 and sf 7..12 (LoRaDemod consumes N samples per symbol)");
+    if (!blocked_supported(static_cast<int>(c->cfg.sf)))
+        return fail(LORA_B200_EINVAL, "stream detection needs sf 7..12");
     if (n_streams > 0x7fffffffu || stream_stride < samples_per_stream) return fail(LORA_B200_EINVAL, "bad batch geometry");
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
@@ -927,6 +927,7 @@ extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_s
     a.iq = reinterpret_cast<const float2*>(d_iq);
     a.stream_stride = stream_stride;
     a.count = samples_per_stream;
+    a.osr = c->cfg.osr; // LoRaDemod consumes N samples per symbol: an oversampled stream is decimated on the fly
     a.n_streams = static_cast<int>(n_streams);
     a.twp = reinterpret_cast<const c64*>(c->d_twp);
     a.tw0 = c->tw0;

@@ -179,7 +179,7 @@ PM_DEV Det detect_window(const StreamDetectArgs& a, const c64* __restrict__ x, c
     c64 in[16], v[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) { // LoRaDemod.cpp:157-160: (samp * chirp) * fineTune, two rounded complex products
-        const c64 s = __ldg(x + t + T * j);
+        const c64 s = __ldg(x + (size_t)(t + T * j) * a.osr);
         const c64 dc = cmul<true>(s, __ldg(chirp + t + T * j), a.one);
         in[j] = cmul<true>(dc, __ldg(a.fine + idx[j]), a.one);
     }
@@ -269,8 +269,9 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
         unsigned sym_count = 0, n_pkt = 0;
         size_t sym_used = 0;
 
-        while (pos + 2 * (size_t)N <= a.count) { // :148
-            Det d = detect_window<SF>(a, x + pos, chirp, fine_idx, fine_err, S, sh, t, slot);
+        const size_t avail = (a.count + a.osr - 1) / a.osr; // samples 0, osr, 2*osr, ... of the stream
+        while (pos + 2 * (size_t)N <= avail) { // :148
+            Det d = detect_window<SF>(a, x + pos * a.osr, chirp, fine_idx, fine_err, S, sh, t, slot);
             const unsigned value = (unsigned)d.value;
             const bool squelched = __fsub_rn(d.power, d.power_avg) < a.thresh; // :174
             size_t total = 0;
@@ -281,7 +282,7 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
                 bool match1 = false;
                 if (syncd && match0) {
                     int ft = fine_idx; // the look-ahead walks a copy (:191-203) but overwrites power/powerAvg/fIndex (:204)
-                    d = detect_window<SF>(a, x + pos + N, chirp, ft, fine_err, S, sh, t, slot);
+                    d = detect_window<SF>(a, x + (pos + N) * a.osr, chirp, ft, fine_err, S, sh, t, slot);
                     match1 = ((unsigned)d.value + 4) / 8 == sync_lo;
                 }
                 if (syncd && match0 && match1) {

@@ -30,6 +30,7 @@ struct StreamResult { // == lora_b200_stream_result
 struct StreamDetectArgs {
     const float2* iq;
     size_t stream_stride, count;
+    size_t osr;       // every osr-th sample is used (plain decimation, as phy.cpp:216 indexes iq[base + i*osr])
     int n_streams;
     const c64* twp;
     Tw0 tw0;

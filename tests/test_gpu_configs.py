@@ -169,7 +169,9 @@ def test_golden_capture_frame_train_is_found(env):
     g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "capture_sf7.npz"))
     x = np.ascontiguousarray(g["iq"][1::2])
     ctx = L.Context(7)
-    sym, pk, res = ctx.stream_detect_batch(torch.from_numpy(x[None]).cuda(), mtu=53, max_packets=32, max_symbols=2048)
+    # the capture as it is (2x oversampled, starting at its second sample) through a context with osr 2 ...
+    sym, pk, res = L.Context(7, osr=2).stream_detect_batch(torch.from_numpy(np.ascontiguousarray(g["iq"][1:])[None]).cuda(),
+                                                           mtu=53, max_packets=32, max_symbols=2048)
     pk, res = L.stream_records(pk, res)
     want, start, err, consumed = ORC.stream_demod(7, x, mtu=53, pkt_cap=32)
     assert int(res[0]["n_packets"]) == len(want) == 15 and int(res[0]["consumed"]) == consumed

@@ -145,9 +145,15 @@ def test_stream_detect_edge_cases(env):
     pk, res = L.stream_records(pk, res)
     assert int(res[0]["n_packets"]) == 3 and int(res[0]["n_symbols"]) == 15
     assert bits(sym.cpu().numpy()[0, :10]) == bits(a.astype(np.int16))
-    # osr != 1 is refused loudly
-    with pytest.raises(L.LoraB200Error):
-        L.Context(sf, osr=2).stream_detect_batch(torch.from_numpy(x[None]).cuda())
+    # an oversampled stream is decimated on the fly: a context with osr 2 sees samples 0, 2, 4, ... and reports
+    # positions in those units, exactly as the oracle does on x[::2]
+    y = np.repeat(x, 2)[: 2 * len(x) - 1]                 # odd length: the last decimated sample is the very last one
+    sym2, pk2, res2 = L.Context(sf, osr=2).stream_detect_batch(torch.from_numpy(y[None]).cuda(), mtu=10)
+    want, start, err, consumed = ORC.stream_demod(sf, y[::2], mtu=10)
+    pk2, res2 = L.stream_records(pk2, res2)
+    assert int(res2[0]["n_packets"]) == len(want) == 3 and int(res2[0]["consumed"]) == consumed
+    assert [int(p["start"]) for p in pk2[0, :3]] == [int(v) for v in start]
+    assert bits(sym2.cpu().numpy()[0, :30]) == bits(np.concatenate(want))
 
 
 def test_stream_detect_repeatable_under_load(env):
