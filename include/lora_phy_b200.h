@@ -253,6 +253,14 @@ int lora_b200_stream_detect_batch(lora_b200_ctx* ctx, const lora_b200_stream_cfg
                                   size_t n_streams, size_t samples_per_stream, size_t stream_stride,
                                   int16_t* d_symbols, lora_b200_stream_packet* d_packets,
                                   lora_b200_stream_result* d_results, void* stream);
+/* LoRaDecoder::work (LoRa-SDR/LoRaDecoder.cpp:196-397) on every packet the synchroniser reported -- in the Pothos
+ * topology LoRaDemod's output port feeds LoRaDecoder's input port.  Slot p = stream * max_packets + k of d_payload
+ * (LORA_B200_PAYLOAD_STRIDE bytes each) and d_chain_results receives packet k of that stream; a slot with no packet
+ * gets n_bytes = -1.  d_symbols / d_packets / d_results are the outputs of lora_b200_stream_detect_batch. */
+int lora_b200_stream_decode_batch(lora_b200_ctx* ctx, const lora_b200_chain_cfg* cfg, const int16_t* d_symbols,
+                                  const lora_b200_stream_packet* d_packets, const lora_b200_stream_result* d_results,
+                                  size_t n_streams, uint32_t max_packets, uint32_t max_symbols, uint8_t* d_payload,
+                                  lora_b200_chain_result* d_chain_results, void* stream);
 
 #ifdef __cplusplus
 }

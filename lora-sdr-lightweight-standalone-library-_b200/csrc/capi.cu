@@ -571,7 +571,8 @@ static int chain_decode_locked(lora_b200_ctx* c, const lora_b200_chain_cfg* g, c
     if (n_packets == 0) return LORA_B200_OK;
     if (n_packets > 0x7fffffffu || symbol_stride < nsym || nsym > 0xffff)
         return fail(LORA_B200_EINVAL, "bad batch geometry");
-    ChainDecodeArgs a{*g, d_symbols, nsym, symbol_stride, d_payload, d_results, c->d_whiten, static_cast<int>(n_packets)};
+    ChainDecodeArgs a{*g, d_symbols, nsym, symbol_stride, d_payload, d_results, c->d_whiten, static_cast<int>(n_packets),
+                      nullptr, nullptr, 0};
     CU(launch_chain_decode(a, st));
     return LORA_B200_OK;
 }
@@ -959,5 +960,24 @@ extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_s
     }
     CU(launch_stream_detect(static_cast<int>(c->cfg.sf), a, c->sm_count, st));
     if (e1) CU(cudaEventRecord(e1, st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_stream_decode_batch(lora_b200_ctx* c, const lora_b200_chain_cfg* g, const int16_t* d_symbols,
+                                             const lora_b200_stream_packet* d_packets,
+                                             const lora_b200_stream_result* d_results, size_t n_streams,
+                                             uint32_t max_packets, uint32_t max_symbols, uint8_t* d_payload,
+                                             lora_b200_chain_result* d_chain_results, void* stream)
+{
+    if (!c || !d_symbols || !d_packets || !d_results || !d_payload || !d_chain_results)
+        return fail(LORA_B200_EINVAL, "null argument");
+    if (int rc = check_chain_cfg(g)) return rc;
+    if (n_streams == 0 || max_packets == 0) return LORA_B200_OK;
+    if (n_streams * static_cast<size_t>(max_packets) > 0x7fffffffu) return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    ChainDecodeArgs a{*g, reinterpret_cast<const uint16_t*>(d_symbols), 0, max_symbols, d_payload, d_chain_results,
+                      c->d_whiten, static_cast<int>(n_streams * max_packets), d_packets, d_results, max_packets};
+    CU(launch_chain_decode(a, static_cast<cudaStream_t>(stream)));
     return LORA_B200_OK;
 }

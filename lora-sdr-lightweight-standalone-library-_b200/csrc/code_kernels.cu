@@ -2,6 +2,7 @@
 // hundred integer ops on <= ~600 symbols, three orders of magnitude below the demod kernel, so the layout
 // is chosen for clarity of parity with LoRa-SDR/LoRaDecoder.cpp rather than for throughput.
 #include "code_kernels.h"
+#include "stream_kernels.h" // StreamPacket / StreamResult records
 #include "demod_kernels.h" // g_launches
 
 namespace lora_b200 {
@@ -230,7 +231,17 @@ __global__ void chain_decode_kernel(ChainDecodeArgs a)
     memset(&r, 0, sizeof(r));
     uint8_t* out = a.payload + (size_t)p * LORA_B200_PAYLOAD_STRIDE;
     const int ppm = g.ppm ? (int)g.ppm : (int)g.sf;
-    const int nin = (int)a.n_symbols;
+    int nin = (int)a.n_symbols;
+    const uint16_t* sym_in = a.symbols + (size_t)p * a.symbol_stride;
+    if (a.stream_packets) {
+        const unsigned st = (unsigned)p / a.pkt_cap, k = (unsigned)p % a.pkt_cap;
+        const StreamResult sr = static_cast<const StreamResult*>(a.stream_results)[st];
+        if (k >= sr.n_packets) { r.n_bytes = -1; a.results[p] = r; return; } // no such packet in this stream
+        const StreamPacket pk = static_cast<const StreamPacket*>(a.stream_packets)[p];
+        const unsigned stored = pk.first_symbol < sr.n_symbols ? sr.n_symbols - pk.first_symbol : 0u;
+        nin = (int)min(pk.n_symbols, stored); // symbols beyond the caller's capacity were counted but not kept
+        sym_in = a.symbols + (size_t)st * a.symbol_stride + pk.first_symbol;
+    }
     if (nin < 8) { r.n_bytes = -2; a.results[p] = r; return; } // :208
     const int rows = 4 + (int)g.rdd;
     const int nsym = ((nin + rows - 1) / rows) * rows; // :210
@@ -238,7 +249,7 @@ __global__ void chain_decode_kernel(ChainDecodeArgs a)
     const int nbytes = (ncw + 1) / 2;                  // :274
 
     CodewordCursor cur;
-    cur.sym = a.symbols + (size_t)p * a.symbol_stride;
+    cur.sym = sym_in;
     cur.whiten = a.whiten;
     cur.nin = nin; cur.nsym = nsym; cur.ncw = ncw; cur.ppm = ppm; cur.cfg_rdd = (int)g.rdd; cur.sf = (int)g.sf;
     cur.explicit_hdr = g.explicit_header;

@@ -36,6 +36,12 @@ struct ChainDecodeArgs { // LoRaDecoder::work, LoRa-SDR/LoRaDecoder.cpp:196-397
     lora_b200_chain_result* results;
     const uint8_t* whiten; // 2 x WHITEN_LEN
     int n_packets;
+    // optional: packets as the stream synchroniser reported them (stream_kernels.h).  Packet slot p = stream * pkt_cap
+    // + k takes its symbols from symbols[stream * symbol_stride + first_symbol ...] and its count from the record;
+    // a slot beyond the stream's packet count yields n_bytes = -1.
+    const void* stream_packets; // StreamPacket[n_streams * pkt_cap]
+    const void* stream_results; // StreamResult[n_streams]
+    unsigned pkt_cap;
 };
 
 struct ChainEncodeArgs { // LoRaEncoder::work, LoRa-SDR/LoRaEncoder.cpp:161-233

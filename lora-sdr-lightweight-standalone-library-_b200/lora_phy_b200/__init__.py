@@ -111,6 +111,8 @@ _SIGNATURES = {
                                                  C.c_uint8, C.c_uint, C.c_void_p, C.c_size_t, C.c_void_p]),
     "lora_b200_stream_detect_batch": (C.c_int, [C.c_void_p, C.POINTER(StreamCfg), C.c_void_p, C.c_size_t, C.c_size_t,
                                                 C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_stream_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(ChainCfg), C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.c_size_t, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 EXPORTS = tuple(_SIGNATURES)
 
@@ -304,6 +306,17 @@ class Context:
         _check(self.lib.lora_b200_stream_detect_batch(self.h, C.byref(cfg), _ptr(iq), n, count, stride, _ptr(sym),
                                                       _ptr(pk), _ptr(res), _stream()))
         return sym, pk, res
+
+    def stream_decode_batch(self, cfg, symbols, packets, results):
+        """LoRaDecoder::work on every packet of stream_detect_batch's output -> (payload u8 [streams, max_packets, 264],
+        chain results u8 [streams, max_packets, 16]); empty slots have n_bytes = -1."""
+        import torch
+        n, max_packets, max_symbols = packets.shape[0], packets.shape[1], symbols.shape[1]
+        payload = torch.zeros((n, max_packets, PAYLOAD_STRIDE), dtype=torch.uint8, device=symbols.device)
+        res = torch.zeros((n, max_packets, 16), dtype=torch.uint8, device=symbols.device)
+        _check(self.lib.lora_b200_stream_decode_batch(self.h, C.byref(cfg), _ptr(symbols), _ptr(packets), _ptr(results), n,
+                                                      max_packets, max_symbols, _ptr(payload), _ptr(res), _stream()))
+        return payload, res
 
     def awgn_batch(self, iq, snr_db, seed=0):
         n, count = iq.shape

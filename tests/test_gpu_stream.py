@@ -188,3 +188,47 @@ def test_stream_detect_repeatable_under_load(env):
     want, start, err, consumed = ORC.stream_demod(sf, base[3], mtu=14, thresh=-8.0)
     pk_h, res_h = L.stream_records(pk, res)
     assert int(res_h[3]["n_packets"]) == len(want) and int(res_h[3]["consumed"]) == consumed
+
+
+@pytest.mark.parametrize("sf,rdd,ppm", [(7, 1, 0), (9, 4, 0), (10, 2, 8)])
+def test_stream_to_payload(env, sf, rdd, ppm):
+    """The whole continuous-stream receiver: payload -> LoRaEncoder -> LoRaMod frame -> channel -> LoRaDemod ->
+    LoRaDecoder -> payload, all on the device, two frames per stream; decoder results equal the oracle's on the
+    symbols the synchroniser delivered."""
+    torch, L, ORC = env["torch"], env["L"], env["ORC"]
+    from _oracle import chain_cfg as orc_cfg
+    n = 1 << sf
+    ctx = L.Context(sf)
+    cfg, oc = L.chain_cfg(sf, rdd, ppm=ppm), orc_cfg(sf, rdd, ppm=ppm)
+    gen = torch.Generator(device="cuda").manual_seed(sf)
+    n_streams = 40
+    pay = torch.randint(0, 256, (2 * n_streams, 24), dtype=torch.uint8, device="cuda", generator=gen)
+    sym = ctx.chain_encode_batch(cfg, pay)
+    nsym = sym.shape[1]
+    fr = ctx.frame_modulate_batch(sym, amplitude=1.0, padding=3)
+    lead = 3 * n
+    x = torch.zeros((n_streams, lead + 2 * (fr.shape[1] + n) + 2 * n), dtype=torch.complex64, device="cuda")
+    x[:, lead:lead + fr.shape[1]] = fr[0::2]
+    x[:, lead + fr.shape[1] + n: lead + 2 * fr.shape[1] + n] = fr[1::2]
+    ctx.awgn_batch(x, torch.full((n_streams,), 12.0, device="cuda"), seed=sf)
+    d_sym, d_pk, d_res = ctx.stream_detect_batch(x, mtu=nsym, thresh_db=-10.0, max_packets=4, max_symbols=4 * nsym)
+    payload, cres = ctx.stream_decode_batch(cfg, d_sym, d_pk, d_res)
+    pk, res = L.stream_records(d_pk, d_res)
+    cres = cres.cpu().numpy().view(L.CHAIN_RESULT).reshape(n_streams, 4)
+    payload, d_sym, pay_h = payload.cpu().numpy(), d_sym.cpu().numpy(), pay.cpu().numpy()
+    good = 0
+    for i in range(n_streams):
+        assert int(res[i]["n_packets"]) >= 2
+        for k in range(4):
+            if k >= int(res[i]["n_packets"]):
+                assert int(cres[i, k]["n_bytes"]) == -1
+                continue
+            s0, cnt = int(pk[i, k]["first_symbol"]), int(pk[i, k]["n_symbols"])
+            ro, bo, info = ORC.chain_decode(oc, d_sym[i, s0:s0 + cnt].astype(np.uint16))
+            assert int(cres[i, k]["n_bytes"]) == ro and int(cres[i, k]["crc_ok"]) == int(info.crc_ok)
+            assert bits(payload[i, k, :max(ro, 0)]) == bits(bo)
+        for k in range(2):
+            if int(cres[i, k]["crc_ok"]) == 1:
+                assert bytes(payload[i, k, :24]) == bytes(pay_h[2 * i + k])
+                good += 1
+    assert good >= 2 * n_streams - 2
