@@ -97,12 +97,12 @@ struct WinParams {
     int down_ofs;
 };
 
-template <int SF>
+template <int SF, bool FAITH, bool OSR1>
 PM_DEV WinParams window_params(const BlockedDemodArgs& a, const PktParams& k, int s)
 {
     constexpr int N = 1 << SF;
     WinParams q;
-    const size_t step = (size_t)N * a.osr;
+    const size_t step = OSR1 ? (size_t)N : (size_t)N * a.osr;
     size_t base = (size_t)s * step;                                              // phy.cpp:205-212
     if (k.t_off > 0) {
         if (base + (size_t)k.t_off + step <= a.count) base += (size_t)k.t_off;
@@ -111,8 +111,11 @@ PM_DEV WinParams window_params(const BlockedDemodArgs& a, const PktParams& k, in
         if (off <= base) base -= off;
     }
     q.base = base;
-    const float toff_f = a.osr == 1 ? (float)k.t_off : __fdiv_rn((float)k.t_off, (float)a.osr);
-    q.start = __fmul_rn(k.rate, __fadd_rn((float)((size_t)s * N), toff_f));      // :213-214
+    const float toff_f = (OSR1 || a.osr == 1) ? (float)k.t_off : __fdiv_rn((float)k.t_off, (float)a.osr);
+    // :213-214.  The fused flavour only uses `start` to widen its trust margin, so it skips the 64-bit conversion
+    // (float(s)*N equals float(s*N) whenever s < 2^24, and any value of that size serves the bound).
+    q.start = FAITH ? __fmul_rn(k.rate, __fadd_rn((float)((size_t)s * N), toff_f))
+                    : k.rate * ((float)s * (float)N + toff_f);
     q.down_ofs = a.dechirp_absolute ? (int)(base & (size_t)(N - 1)) : 0;
     return q;
 }
@@ -174,11 +177,11 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
         int rot_ofs = -1;
         c64 rot[16];
         for (; s < s_end; ++s) {
-            const WinParams q = window_params<SF>(a, pk_, s);
+            const WinParams q = window_params<SF, FAITH, OSR1>(a, pk_, s);
             const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
             const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
             if (!LIST && t == 0) { // the samples right after this window: the next window of the run, or of the packet
-                const size_t span = (size_t)N * a.osr;
+                const size_t span = OSR1 ? (size_t)N : (size_t)N * a.osr;
                 const size_t left = a.count - min(a.count, q.base + span);
                 l2_prefetch(x + span, sizeof(c64) * min(span, left));
             }

@@ -36,12 +36,18 @@ struct Blk {
     static constexpr int T = N / 16;         // threads per window
     static constexpr int NP = (L + 1) / 2;   // passes
     __host__ __device__ static constexpr int radix(int s) { return s < L4 ? 4 : 2; }
-    __host__ __device__ static constexpr int m(int s) { int p = 1; for (int u = 0; u <= s; ++u) p *= radix(u); return N / p; }
-    __host__ __device__ static constexpr int F(int s) { int p = 1; for (int u = 0; u < s; ++u) p *= radix(u); return p; }
+    // Closed forms (shifts only).  Written as product loops with a division, these reached ptxas as run-time
+    // divisions by 16 and 64 inside the window loop (I2F/MUFU.RCP/IMAD.HI sequences in the SASS); the loop forms are
+    // kept below as m_ref/F_ref/toff_ref and compared by static_assert.
+    __host__ __device__ static constexpr int lp(int s) { return s < L4 ? 2 * (s + 1) : 2 * L4 + (s - L4 + 1); } // log2(r_0..r_s)
+    __host__ __device__ static constexpr int m(int s) { return N >> lp(s); }
+    __host__ __device__ static constexpr int F(int s) { return s == 0 ? 1 : 1 << lp(s - 1); }
+    static constexpr int m_ref(int s) { int p = 1; for (int u = 0; u <= s; ++u) p *= radix(u); return N / p; }
+    static constexpr int F_ref(int s) { int p = 1; for (int u = 0; u < s; ++u) p *= radix(u); return p; }
     // pass p (0 = innermost, executed first) covers stages pa(p)..pb(p)
     __host__ __device__ static constexpr int pb(int p) { return L - 1 - 2 * p; }
     __host__ __device__ static constexpr int pa(int p) { return pb(p) >= 1 ? pb(p) - 1 : 0; }
-    __host__ __device__ static constexpr int R(int p) { int r = 1; for (int s = pa(p); s <= pb(p); ++s) r *= radix(s); return r; }
+    __host__ __device__ static constexpr int R(int p) { return pa(p) == pb(p) ? radix(pb(p)) : radix(pa(p)) * radix(pb(p)); }
     __host__ __device__ static constexpr int G(int p) { return 16 / R(p); }
     __host__ __device__ static constexpr int pad(int X)
     {
@@ -53,19 +59,40 @@ struct Blk {
     // Per-stage twiddle table: stage s, multiplier q (1..radix-1), k in [0, m_s) lives at toff(s) + (q-1)*m_s + k
     // and holds tw[k*F_s*q] -- the same values kissfft indexes, laid out so that the threads of a window (consecutive
     // k) read consecutive entries.
-    __host__ __device__ static constexpr int toff(int s) { int o = 0; for (int u = 0; u < s; ++u) o += (radix(u) - 1) * m(u); return o; }
+    // = sum over u < s of (radix(u) - 1) * m(u); every stage before the last is radix 4, so the sum telescopes
+    __host__ __device__ static constexpr int toff(int s) { return N - (N >> (2 * s)); }
+    static constexpr int toff_ref(int s) { int o = 0; for (int u = 0; u < s; ++u) o += (radix(u) - 1) * m_ref(u); return o; }
     static constexpr int TWP = N + 16; // entries allocated (the table needs N-1, or N for odd SF)
     // digit of element e (position order inside the pass) at stage s
-    __host__ __device__ static constexpr int digit(int p, int s, int e) { return (e / (m(s) / m(pb(p)))) % radix(s); }
+    __host__ __device__ static constexpr int digit(int p, int s, int e) { return (e >> (lp(pb(p)) - lp(s))) & (radix(s) - 1); }
     // pass 0: register slot of the j-th loaded sample (input index t + T*j)
     __host__ __device__ static constexpr int slot0(int j)
     {
         const int g = j % G(0), jj = j / G(0);
         int e = 0, rem = jj;
-        for (int s = pa(0); s <= pb(0); ++s) { e += (rem % radix(s)) * (m(s) / m(pb(0))); rem /= radix(s); }
+        for (int s = pa(0); s <= pb(0); ++s) { e += (rem & (radix(s) - 1)) << (lp(pb(0)) - lp(s)); rem >>= (radix(s) == 4 ? 2 : 1); }
         return g * R(0) + e;
     }
 };
+
+template <int SF>
+constexpr bool blk_closed_forms_ok()
+{
+    using B = Blk<SF>;
+    for (int s = 0; s < B::L; ++s)
+        if (B::m(s) != B::m_ref(s) || B::F(s) != B::F_ref(s) || B::toff(s) != B::toff_ref(s)) return false;
+    for (int p = 0; p < B::NP; ++p) {
+        int r = 1;
+        for (int s = B::pa(p); s <= B::pb(p); ++s) r *= B::radix(s);
+        if (r != B::R(p)) return false;
+        for (int s = B::pa(p); s <= B::pb(p); ++s)
+            for (int e = 0; e < 16; ++e)
+                if (B::digit(p, s, e) != (e / (B::m_ref(s) / B::m_ref(B::pb(p)))) % B::radix(s)) return false;
+    }
+    return true;
+}
+static_assert(blk_closed_forms_ok<7>() && blk_closed_forms_ok<8>() && blk_closed_forms_ok<9>() && blk_closed_forms_ok<10>() &&
+              blk_closed_forms_ok<11>() && blk_closed_forms_ok<12>(), "closed forms of the stage geometry");
 
 // The 16 twiddles pass 0 can need, tw0[k*4+q] = tw[k * F(pa(0)) * q]; thread-independent, so they travel as
 // kernel arguments (constant bank) instead of being loaded.
@@ -106,7 +133,7 @@ PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restric
     constexpr int a = B::pa(P), b = B::pb(P), Rp = B::R(P), Gp = B::G(P), mb = B::m(b);
 #pragma unroll
     for (int s = b; s >= a; --s) {
-        const int w = B::m(s) / mb;      // register stride of this stage's digit
+        const int w = 1 << (B::lp(b) - B::lp(s)); // = m(s) / mb, register stride of this stage's digit
         const int rs = B::radix(s);
 #pragma unroll
         for (int g = 0; g < Gp; ++g) {
