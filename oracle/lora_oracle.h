@@ -140,6 +140,30 @@ typedef struct {
 long   orc_chain_decode(const orc_chain_cfg* c, const uint16_t* symbols, size_t nsym,
                         uint8_t* out, size_t cap, orc_chain_info* info);
 
+/* ---- the LoRa coding chain as deployed on the air (std_chain.c) ---------------------
+ * Not in the reference: pinned by the 16 CRC-checked frames of the reference's golden capture, see std_chain.c. */
+typedef struct {
+    unsigned sf;            /* 7..12 */
+    unsigned cr;            /* 1..4 = 4/5 .. 4/8 (explicit header: decoder takes it from the header) */
+    int ldro;               /* low data rate optimisation: every block at sf-2 bits per symbol */
+    int implicit_header;
+    int has_crc;            /* encoder; decoder in implicit-header mode */
+    unsigned payload_len;   /* decoder, implicit-header mode */
+} orc_std_cfg;
+typedef struct {
+    int n_bytes;            /* payload bytes; -1 header invalid, -2 fewer than 8 symbols / bad cfg, -3 frame truncated */
+    int hdr_ok, hdr_length, hdr_cr, has_crc, crc_ok;
+    int corrected, uncorrectable; /* some codeword had one bit corrected / an error that could not be */
+    int symbols_used;
+} orc_std_info;
+uint8_t  orc_std_header_checksum(unsigned n0, unsigned n1, unsigned n2);
+void     orc_std_whitening(uint8_t* seq, size_t n);
+uint16_t orc_std_crc(const uint8_t* payload, size_t len);
+size_t   orc_std_symbol_count(const orc_std_cfg* c, size_t len);
+size_t   orc_std_encode(const orc_std_cfg* c, const uint8_t* payload, size_t len, uint16_t* out, size_t cap);
+long     orc_std_decode(const orc_std_cfg* c, const uint16_t* symbols, size_t nsym, uint8_t* out, size_t cap,
+                        orc_std_info* info);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,17 @@ class ChainCfg(C.Structure):
                 ("error_check", C.c_int), ("hdr_out", C.c_int), ("data_length", C.c_uint)]
 
 
+class StdCfg(C.Structure):
+    """The deployed LoRa coding chain (oracle/std_chain.c; same layout as lora_b200_std_cfg)."""
+    _fields_ = [("sf", C.c_uint), ("cr", C.c_uint), ("ldro", C.c_int), ("implicit_header", C.c_int),
+                ("has_crc", C.c_int), ("payload_len", C.c_uint)]
+
+
+class StdInfo(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("n_bytes", "hdr_ok", "hdr_length", "hdr_cr", "has_crc", "crc_ok", "corrected",
+                                        "uncorrectable", "symbols_used")]
+
+
 class ChainInfo(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("drop_line", "parity_error", "uncorrectable", "hdr_length",
                                         "hdr_has_crc", "hdr_rdd", "hdr_checksum", "crc_present", "crc_ok")]
@@ -217,6 +228,37 @@ class Lib:
         return int(r), out[:max(r, 0)], info
 
 
+    # ---- the deployed LoRa coding chain (oracle/std_chain.c) ------------------------------------------
+    def std_symbol_count(self, cfg, length):
+        return self.fn("std_symbol_count", C.c_size_t, [C.POINTER(StdCfg), C.c_size_t])(C.byref(cfg), length)
+
+    def std_encode(self, cfg, payload):
+        payload = np.ascontiguousarray(payload, np.uint8)
+        n = self.std_symbol_count(cfg, len(payload))
+        out = np.zeros(max(n, 1), np.uint16)
+        arg = payload if len(payload) else np.zeros(1, np.uint8)
+        r = self.fn("std_encode", C.c_size_t, [C.POINTER(StdCfg), u8p, C.c_size_t, u16p, C.c_size_t])(
+            C.byref(cfg), arg, len(payload), out, n)
+        return out[:r]
+
+    def std_decode(self, cfg, symbols):
+        """-> (ret, bytes, StdInfo)"""
+        symbols = np.ascontiguousarray(symbols, np.uint16)
+        arg = symbols if len(symbols) else np.zeros(1, np.uint16)
+        out = np.zeros(256, np.uint8)
+        info = StdInfo()
+        r = self.fn("std_decode", C.c_long, [C.POINTER(StdCfg), u16p, C.c_size_t, u8p, C.c_size_t, C.POINTER(StdInfo)])(
+            C.byref(cfg), arg, len(symbols), out, len(out), C.byref(info))
+        return int(r), out[:max(r, 0)], info
+
+    def std_header_checksum(self, n0, n1, n2):
+        return int(self.fn("std_header_checksum", C.c_ubyte, [C.c_uint, C.c_uint, C.c_uint])(n0, n1, n2))
+
+    def std_crc(self, payload):
+        payload = np.ascontiguousarray(payload, np.uint8)
+        arg = payload if len(payload) else np.zeros(1, np.uint8)
+        return int(self.fn("std_crc", C.c_ushort, [u8p, C.c_size_t])(arg, len(payload)))
+
     # ---- upstream Pothos blocks restated (oracle/stream.c) -------------------------------------------
     def frame_modulate(self, sf, symbols, sync=0x12, padding=1, ampl=0.3, ovs=1):
         symbols = np.ascontiguousarray(symbols, np.uint16)
@@ -256,6 +298,10 @@ def chain_cfg(sf, rdd, ppm=0, explicit=True, crc=True, whitening=True, interleav
               error_check=False, hdr_out=False, data_length=8):
     return ChainCfg(sf, ppm, rdd, int(explicit), int(crc), int(whitening), int(interleaving),
                     int(error_check), int(hdr_out), data_length)
+
+
+def std_cfg(sf, cr=1, ldro=False, implicit=False, crc=True, payload_len=0):
+    return StdCfg(sf, cr, int(ldro), int(implicit), int(crc), payload_len)
 
 
 def _load(path, prefix):
