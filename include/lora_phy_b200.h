@@ -92,6 +92,30 @@ typedef struct {
 
 #define LORA_B200_PAYLOAD_STRIDE 264 /* bytes reserved per packet by the chain decoder (<= 255+3+2, padded) */
 
+/* The LoRa coding chain as it is deployed on the air (not in the reference, whose chain is the
+ * SX127x-style variant of the Pothos blocks above): symbol = bin - 1, first eight symbols at reduced rate (sf-2 bits,
+ * CR 4/8) carrying the explicit header, diagonal interleaver, Hamming 4/5..4/8, whitening LFSR x^8+x^6+x^5+x^4+1,
+ * CRC-16/CCITT with the last two payload bytes folded in.  It decodes the standards-style frames of the reference's
+ * golden capture (vectors_binary/bw_125k_sf_7_cr_1_...unknown), which rx_runner cannot. */
+typedef struct {
+    unsigned sf;            /* 7..12                                                                    */
+    unsigned cr;            /* 1..4 = 4/5..4/8; an explicit header overrides it on receive               */
+    int ldro;               /* low-data-rate optimisation: every block carries sf-2 bits per symbol      */
+    int implicit_header;
+    int has_crc;            /* encoder; decoder in implicit-header mode                                  */
+    unsigned payload_len;   /* decoder, implicit-header mode                                             */
+} lora_b200_std_cfg;
+
+/* Per-packet result of the deployed-chain decoder, 16 bytes. */
+typedef struct {
+    int16_t n_bytes;        /* payload bytes; -1 header invalid (or no such packet), -2 fewer than 8 symbols, -3 truncated */
+    uint16_t symbols_used;  /* symbols of the frame actually consumed                                   */
+    uint8_t hdr_ok, hdr_length, hdr_cr, has_crc, crc_ok;
+    uint8_t corrected;      /* some codeword had one bit corrected                                      */
+    uint8_t uncorrectable;  /* some codeword had an error that could only be detected                   */
+    uint8_t reserved[5];
+} lora_b200_std_result;
+
 /* ---- lifetime ------------------------------------------------------------------------------------------ */
 /* Replaces lora_phy::init (phy.cpp:26-49) / lora_demod_init (LoRaDemod.cpp:10-32): builds the twiddle,
  * down-chirp and window tables on the host exactly as the reference does and uploads them. */
@@ -261,6 +285,20 @@ int lora_b200_stream_decode_batch(lora_b200_ctx* ctx, const lora_b200_chain_cfg*
                                   const lora_b200_stream_packet* d_packets, const lora_b200_stream_result* d_results,
                                   size_t n_streams, uint32_t max_packets, uint32_t max_symbols, uint8_t* d_payload,
                                   lora_b200_chain_result* d_chain_results, void* stream);
+
+/* Deployed-chain counterparts of lora_b200_chain_decode_batch / _encode_batch / lora_b200_stream_decode_batch.
+ * d_payload: LORA_B200_PAYLOAD_STRIDE bytes per packet.  The encoder with d_symbols == NULL only reports the symbol
+ * count.  In the stream form the symbols are the synchroniser's int16 bins (taken modulo 2^sf). */
+int lora_b200_std_decode_batch(lora_b200_ctx* ctx, const lora_b200_std_cfg* cfg, const uint16_t* d_symbols,
+                               size_t n_packets, size_t nsym, size_t symbol_stride, uint8_t* d_payload,
+                               lora_b200_std_result* d_results, void* stream);
+int lora_b200_std_encode_batch(lora_b200_ctx* ctx, const lora_b200_std_cfg* cfg, const uint8_t* d_payload,
+                               size_t n_packets, size_t payload_len, size_t payload_stride, uint16_t* d_symbols,
+                               size_t symbol_stride, size_t* symbols_per_packet, void* stream);
+int lora_b200_std_stream_decode_batch(lora_b200_ctx* ctx, const lora_b200_std_cfg* cfg, const int16_t* d_symbols,
+                                      const lora_b200_stream_packet* d_packets, const lora_b200_stream_result* d_results,
+                                      size_t n_streams, uint32_t max_packets, uint32_t max_symbols, uint8_t* d_payload,
+                                      lora_b200_std_result* d_std_results, void* stream);
 
 #ifdef __cplusplus
 }

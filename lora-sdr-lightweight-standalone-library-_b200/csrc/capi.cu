@@ -22,6 +22,7 @@
 #include "demod_kernels.h"
 #include "host_tables.h"
 #include "mod_kernels.h"
+#include "std_kernels.h"
 #include "stream_kernels.h"
 
 using namespace lora_b200;
@@ -610,6 +611,74 @@ extern "C" int lora_b200_chain_encode_batch(lora_b200_ctx* c, const lora_b200_ch
     ChainEncodeArgs a{*g, d_payload, payload_len, payload_stride, d_symbols, symbol_stride, c->d_whiten,
                       static_cast<int>(n_packets)};
     CU(launch_chain_encode(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+// ---- deployed LoRa coding chain (std_kernels.cu) ---------------------------------------------------------------
+static int check_std_cfg(const lora_b200_std_cfg* g)
+{
+    if (!g) return fail(LORA_B200_EINVAL, "null chain config");
+    if (g->sf < 7 || g->sf > 12) return fail(LORA_B200_EINVAL, "sf must be 7..12");
+    if (g->cr < 1 || g->cr > 4) return fail(LORA_B200_EINVAL, "cr must be 1..4 (4/5..4/8)");
+    if (g->payload_len > 255) return fail(LORA_B200_EINVAL, "payload_len > 255");
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_std_decode_batch(lora_b200_ctx* c, const lora_b200_std_cfg* g, const uint16_t* d_symbols,
+                                          size_t n_packets, size_t nsym, size_t symbol_stride, uint8_t* d_payload,
+                                          lora_b200_std_result* d_results, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (int rc = check_std_cfg(g)) return rc;
+    if (!d_symbols || !d_payload || !d_results) return fail(LORA_B200_EINVAL, "null buffer");
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || symbol_stride < nsym || nsym > 0xffff) return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    StdDecodeArgs a{*g, d_symbols, nsym, symbol_stride, d_payload, d_results, static_cast<int>(n_packets), nullptr, nullptr, 0};
+    CU(launch_std_decode(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_std_encode_batch(lora_b200_ctx* c, const lora_b200_std_cfg* g, const uint8_t* d_payload,
+                                          size_t n_packets, size_t payload_len, size_t payload_stride,
+                                          uint16_t* d_symbols, size_t symbol_stride, size_t* symbols_per_packet,
+                                          void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (int rc = check_std_cfg(g)) return rc;
+    if (payload_len > 255) return fail(LORA_B200_EINVAL, "payload longer than 255 bytes");
+    const size_t nsym = std_symbol_count(*g, payload_len);
+    if (nsym == 0) return fail(LORA_B200_EINVAL, "invalid chain configuration");
+    if (symbols_per_packet) *symbols_per_packet = nsym;
+    if (!d_symbols) return LORA_B200_OK; // size query
+    if (!d_payload && payload_len) return fail(LORA_B200_EINVAL, "null payload");
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > 0x7fffffffu || symbol_stride < nsym || payload_stride < payload_len)
+        return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    StdEncodeArgs a{*g, d_payload, payload_len, payload_stride, d_symbols, nsym, symbol_stride, static_cast<int>(n_packets)};
+    CU(launch_std_encode(a, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_std_stream_decode_batch(lora_b200_ctx* c, const lora_b200_std_cfg* g, const int16_t* d_symbols,
+                                                 const lora_b200_stream_packet* d_packets,
+                                                 const lora_b200_stream_result* d_results, size_t n_streams,
+                                                 uint32_t max_packets, uint32_t max_symbols, uint8_t* d_payload,
+                                                 lora_b200_std_result* d_std_results, void* stream)
+{
+    if (!c || !d_symbols || !d_packets || !d_results || !d_payload || !d_std_results)
+        return fail(LORA_B200_EINVAL, "null argument");
+    if (int rc = check_std_cfg(g)) return rc;
+    if (n_streams == 0 || max_packets == 0) return LORA_B200_OK;
+    if (n_streams * static_cast<size_t>(max_packets) > 0x7fffffffu) return fail(LORA_B200_EINVAL, "bad batch geometry");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    StdDecodeArgs a{*g, reinterpret_cast<const uint16_t*>(d_symbols), 0, max_symbols, d_payload, d_std_results,
+                    static_cast<int>(n_streams * max_packets), d_packets, d_results, max_packets};
+    CU(launch_std_decode(a, static_cast<cudaStream_t>(stream)));
     return LORA_B200_OK;
 }
 

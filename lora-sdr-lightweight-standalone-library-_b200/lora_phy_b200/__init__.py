@@ -38,7 +38,16 @@ CHAIN_RESULT = np.dtype([("n_bytes", "<i2"), ("drop_line", "<i2"), ("parity_erro
                          ("uncorrectable", "u1"), ("hdr_length", "u1"), ("hdr_has_crc", "u1"),
                          ("hdr_rdd", "u1"), ("hdr_checksum", "u1"), ("crc_present", "u1"), ("crc_ok", "u1"),
                          ("reserved", "u1", 4)])
-assert PKT_METRICS.itemsize == 16 and CHAIN_RESULT.itemsize == 16
+class StdCfg(C.Structure):
+    """lora_b200_std_cfg: the LoRa coding chain as deployed on the air (csrc/std_kernels.cu)."""
+    _fields_ = [("sf", C.c_uint), ("cr", C.c_uint), ("ldro", C.c_int), ("implicit_header", C.c_int),
+                ("has_crc", C.c_int), ("payload_len", C.c_uint)]
+
+
+STD_RESULT = np.dtype([("n_bytes", "<i2"), ("symbols_used", "<u2"), ("hdr_ok", "u1"), ("hdr_length", "u1"),
+                       ("hdr_cr", "u1"), ("has_crc", "u1"), ("crc_ok", "u1"), ("corrected", "u1"),
+                       ("uncorrectable", "u1"), ("reserved", "u1", (5,))])
+assert PKT_METRICS.itemsize == 16 and CHAIN_RESULT.itemsize == 16 and STD_RESULT.itemsize == 16
 
 
 class StreamCfg(C.Structure):  # lora_b200_stream_cfg
@@ -54,6 +63,10 @@ STREAM_RESULT = np.dtype([("consumed", "<u8"), ("n_packets", "<u4"), ("n_symbols
 
 class LoraB200Error(RuntimeError):
     pass
+
+
+def std_cfg(sf, cr=1, ldro=False, implicit=False, crc=True, payload_len=0):
+    return StdCfg(sf, cr, int(ldro), int(implicit), int(crc), payload_len)
 
 
 def chain_cfg(sf, rdd, ppm=0, explicit=True, crc=True, whitening=True, interleaving=True,
@@ -73,6 +86,13 @@ _SIGNATURES = {
     "lora_b200_kernel_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]),
     "lora_b200_set_precision": (C.c_int, [C.c_void_p, C.c_int]),
     "lora_b200_set_overlap": (C.c_int, [C.c_void_p, C.c_int]),
+    "lora_b200_std_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(StdCfg), C.c_void_p, C.c_size_t, C.c_size_t,
+                                             C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_std_encode_batch": (C.c_int, [C.c_void_p, C.POINTER(StdCfg), C.c_void_p, C.c_size_t, C.c_size_t,
+                                             C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p]),
+    "lora_b200_std_stream_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(StdCfg), C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_size_t, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p]),
     "lora_b200_recheck_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
     "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
@@ -316,6 +336,42 @@ class Context:
         res = torch.zeros((n, max_packets, 16), dtype=torch.uint8, device=symbols.device)
         _check(self.lib.lora_b200_stream_decode_batch(self.h, C.byref(cfg), _ptr(symbols), _ptr(packets), _ptr(results), n,
                                                       max_packets, max_symbols, _ptr(payload), _ptr(res), _stream()))
+        return payload, res
+
+    # ---- the deployed LoRa coding chain (csrc/std_kernels.cu) -----------------------
+    def std_symbol_count(self, cfg, payload_len):
+        k = C.c_size_t()
+        _check(self.lib.lora_b200_std_encode_batch(self.h, C.byref(cfg), None, 0, payload_len, payload_len, None, 0,
+                                                   C.byref(k), None))
+        return k.value
+
+    def std_encode_batch(self, cfg, payload):
+        import torch
+        n, plen = payload.shape
+        sym = torch.zeros((n, self.std_symbol_count(cfg, plen)), dtype=torch.int16, device=payload.device)
+        _check(self.lib.lora_b200_std_encode_batch(self.h, C.byref(cfg), _ptr(payload), n, plen, payload.stride(0),
+                                                   _ptr(sym), sym.stride(0), None, _stream()))
+        return sym
+
+    def std_decode_batch(self, cfg, symbols):
+        """-> (payload u8 [n, 264], results u8 [n, 16] viewed as STD_RESULT)"""
+        import torch
+        n, nsym = symbols.shape
+        payload = torch.zeros((n, PAYLOAD_STRIDE), dtype=torch.uint8, device=symbols.device)
+        res = torch.zeros((n, 16), dtype=torch.uint8, device=symbols.device)
+        _check(self.lib.lora_b200_std_decode_batch(self.h, C.byref(cfg), _ptr(symbols), n, nsym, symbols.stride(0),
+                                                   _ptr(payload), _ptr(res), _stream()))
+        return payload, res
+
+    def std_stream_decode_batch(self, cfg, symbols, packets, results):
+        """The deployed chain on every packet of stream_detect_batch's output (layout as stream_decode_batch)."""
+        import torch
+        n, max_packets, max_symbols = packets.shape[0], packets.shape[1], symbols.shape[1]
+        payload = torch.zeros((n, max_packets, PAYLOAD_STRIDE), dtype=torch.uint8, device=symbols.device)
+        res = torch.zeros((n, max_packets, 16), dtype=torch.uint8, device=symbols.device)
+        _check(self.lib.lora_b200_std_stream_decode_batch(self.h, C.byref(cfg), _ptr(symbols), _ptr(packets),
+                                                          _ptr(results), n, max_packets, max_symbols, _ptr(payload),
+                                                          _ptr(res), _stream()))
         return payload, res
 
     def awgn_batch(self, iq, snr_db, seed=0):
