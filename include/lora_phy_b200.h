@@ -299,6 +299,16 @@ int lora_b200_std_stream_decode_batch(lora_b200_ctx* ctx, const lora_b200_std_cf
                                       const lora_b200_stream_packet* d_packets, const lora_b200_stream_result* d_results,
                                       size_t n_streams, uint32_t max_packets, uint32_t max_symbols, uint8_t* d_payload,
                                       lora_b200_std_result* d_std_results, void* stream);
+/* One capture, host buffers in and out: copy in, frame synchroniser (decimating by the context's osr), deployed chain,
+ * copy out.  h_payload: cfg->max_packets x LORA_B200_PAYLOAD_STRIDE bytes; h_results: cfg->max_packets; h_packets
+ * (optional): cfg->max_packets records; *n_packets: packets stored.  stream_cfg->mtu = 0 takes the frame length from
+ * the capture: a first pass stops after every header block, the second collects the longest frame a valid header
+ * announced (frames shorter than that must be followed by at least the difference of silence).
+ * bin/lora_rx_stream is this call behind a CLI. */
+int lora_b200_std_receive_stream_host(lora_b200_ctx* ctx, const lora_b200_std_cfg* cfg,
+                                      const lora_b200_stream_cfg* stream_cfg, const lora_b200_c32* h_iq, size_t count,
+                                      uint8_t* h_payload, lora_b200_std_result* h_results,
+                                      lora_b200_stream_packet* h_packets, uint32_t* n_packets);
 
 #ifdef __cplusplus
 }

@@ -969,20 +969,16 @@ extern "C" int lora_b200_frame_modulate_batch(lora_b200_ctx* c, const uint16_t* 
     return LORA_B200_OK;
 }
 
-extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_stream_cfg* cfg, const lora_b200_c32* d_iq,
-                                             size_t n_streams, size_t samples_per_stream, size_t stream_stride,
-                                             int16_t* d_symbols, lora_b200_stream_packet* d_packets,
-                                             lora_b200_stream_result* d_results, void* stream)
+static int stream_detect_locked(lora_b200_ctx* c, const lora_b200_stream_cfg* cfg, const lora_b200_c32* d_iq,
+                                size_t n_streams, size_t samples_per_stream, size_t stream_stride, int16_t* d_symbols,
+                                lora_b200_stream_packet* d_packets, lora_b200_stream_result* d_results, cudaStream_t st)
 {
-    if (!c || !cfg || !d_results) return fail(LORA_B200_EINVAL, "null argument");
+    if (!cfg || !d_results) return fail(LORA_B200_EINVAL, "null argument");
     if (n_streams == 0) return LORA_B200_OK;
     if (!d_iq || (!d_symbols && cfg->max_symbols) || (!d_packets && cfg->max_packets)) return fail(LORA_B200_EINVAL, "null argument");
     if (!blocked_supported(static_cast<int>(c->cfg.sf)))
         return fail(LORA_B200_EINVAL, "stream detection needs sf 7..12");
     if (n_streams > 0x7fffffffu || stream_stride < samples_per_stream) return fail(LORA_B200_EINVAL, "bad batch geometry");
-    std::lock_guard<std::mutex> lk(c->mu);
-    CU(cudaSetDevice(c->device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t n = static_cast<size_t>(c->n);
     if (!c->d_stream_tables) {
         std::vector<float2> up, down, fine;
@@ -1029,6 +1025,84 @@ extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_s
     }
     CU(launch_stream_detect(static_cast<int>(c->cfg.sf), a, c->sm_count, st));
     if (e1) CU(cudaEventRecord(e1, st));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_stream_detect_batch(lora_b200_ctx* c, const lora_b200_stream_cfg* cfg, const lora_b200_c32* d_iq,
+                                             size_t n_streams, size_t samples_per_stream, size_t stream_stride,
+                                             int16_t* d_symbols, lora_b200_stream_packet* d_packets,
+                                             lora_b200_stream_result* d_results, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null argument");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return stream_detect_locked(c, cfg, d_iq, n_streams, samples_per_stream, stream_stride, d_symbols, d_packets, d_results,
+                                static_cast<cudaStream_t>(stream));
+}
+
+// One capture, host to host: copy in, frame synchroniser, deployed coding chain, copy out.
+extern "C" int lora_b200_std_receive_stream_host(lora_b200_ctx* c, const lora_b200_std_cfg* g,
+                                                 const lora_b200_stream_cfg* cfg, const lora_b200_c32* h_iq, size_t count,
+                                                 uint8_t* h_payload, lora_b200_std_result* h_results,
+                                                 lora_b200_stream_packet* h_packets, uint32_t* n_packets)
+{
+    if (!c || !cfg || !h_iq || !h_payload || !h_results || !n_packets) return fail(LORA_B200_EINVAL, "null argument");
+    if (int rc = check_std_cfg(g)) return rc;
+    if (cfg->max_packets == 0 || cfg->max_symbols == 0) return fail(LORA_B200_EINVAL, "no room for packets");
+    *n_packets = 0;
+    if (count == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const size_t np = cfg->max_packets;
+    CU(c->s_iq.reserve(sizeof(float2) * count));
+    CU(c->s_sym.reserve(sizeof(int16_t) * cfg->max_symbols));
+    CU(c->s_misc.reserve(sizeof(lora_b200_stream_packet) * np + sizeof(lora_b200_stream_result)));
+    CU(c->s_payload.reserve(static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * np));
+    CU(c->s_results.reserve(sizeof(lora_b200_std_result) * np));
+    lora_b200_stream_result* d_res = c->s_misc.as<lora_b200_stream_result>();
+    lora_b200_stream_packet* d_pk = reinterpret_cast<lora_b200_stream_packet*>(d_res + 1);
+    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count, cudaMemcpyHostToDevice, st));
+    lora_b200_stream_cfg sc = *cfg;
+    StdDecodeArgs a{*g, c->s_sym.as<uint16_t>(), 0, cfg->max_symbols, c->s_payload.as<uint8_t>(),
+                    c->s_results.as<lora_b200_std_result>(), static_cast<int>(np), d_pk, d_res, cfg->max_packets};
+    if (sc.mtu == 0) {
+        // The synchroniser (LoRaDemod.cpp:286-310) collects data symbols until `mtu` or a squelched window; it does not
+        // read the header.  mtu = 0 asks for the frame length to be taken from the capture itself: a first pass that
+        // stops after every header block, then the longest frame any valid header announces.
+        if (g->implicit_header) {
+            sc.mtu = static_cast<uint32_t>(std_symbol_count(*g, g->payload_len));
+        } else {
+            sc.mtu = 8;
+            if (int rc = stream_detect_locked(c, &sc, c->s_iq.as<lora_b200_c32>(), 1, count, count, c->s_sym.as<int16_t>(),
+                                              d_pk, d_res, st))
+                return rc;
+            CU(launch_std_decode(a, st));
+            CU(cudaMemcpyAsync(h_results, c->s_results.p, sizeof(lora_b200_std_result) * np, cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            size_t longest = 0;
+            for (size_t k = 0; k < np; ++k) {
+                const lora_b200_std_result& r = h_results[k];
+                if (r.n_bytes != -3 || !r.hdr_ok) continue; // -3: header valid, frame cut short by mtu
+                lora_b200_std_cfg f = *g;
+                f.cr = r.hdr_cr; f.has_crc = r.has_crc;
+                longest = std::max(longest, std_symbol_count(f, r.hdr_length));
+            }
+            if (longest == 0) return LORA_B200_OK; // no frame with a valid header
+            sc.mtu = static_cast<uint32_t>(longest);
+        }
+    }
+    if (int rc = stream_detect_locked(c, &sc, c->s_iq.as<lora_b200_c32>(), 1, count, count, c->s_sym.as<int16_t>(), d_pk,
+                                      d_res, st))
+        return rc;
+    CU(launch_std_decode(a, st));
+    lora_b200_stream_result res{};
+    CU(cudaMemcpyAsync(&res, d_res, sizeof(res), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h_payload, c->s_payload.p, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * np, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h_results, c->s_results.p, sizeof(lora_b200_std_result) * np, cudaMemcpyDeviceToHost, st));
+    if (h_packets) CU(cudaMemcpyAsync(h_packets, d_pk, sizeof(lora_b200_stream_packet) * np, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    *n_packets = res.n_packets < cfg->max_packets ? res.n_packets : cfg->max_packets;
     return LORA_B200_OK;
 }
 

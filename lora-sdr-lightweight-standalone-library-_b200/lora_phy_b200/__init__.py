@@ -93,6 +93,8 @@ _SIGNATURES = {
     "lora_b200_std_stream_decode_batch": (C.c_int, [C.c_void_p, C.POINTER(StdCfg), C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_size_t, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                                     C.c_void_p]),
+    "lora_b200_std_receive_stream_host": (C.c_int, [C.c_void_p, C.POINTER(StdCfg), C.c_void_p, C.c_void_p, C.c_size_t,
+                                                    C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
     "lora_b200_recheck_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
     "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
@@ -373,6 +375,21 @@ class Context:
                                                           _ptr(results), n, max_packets, max_symbols, _ptr(payload),
                                                           _ptr(res), _stream()))
         return payload, res
+
+    def std_receive_stream_host(self, cfg, iq, sync=0x12, thresh_db=-30.0, mtu=0, max_packets=64):
+        """One host capture -> (list of payload bytes, STD_RESULT records, STREAM_PACKET records); mtu 0 = from the headers."""
+        iq = np.ascontiguousarray(iq, np.complex64)
+        sc = StreamCfg(sync, thresh_db, mtu, max_packets, len(iq) // self.step + 8)
+        payload = np.zeros((max_packets, PAYLOAD_STRIDE), np.uint8)
+        res = np.zeros(max_packets, STD_RESULT)
+        pk = np.zeros(max_packets, STREAM_PACKET)
+        n = C.c_uint32()
+        _check(self.lib.lora_b200_std_receive_stream_host(self.h, C.byref(cfg), C.byref(sc), iq.ctypes.data_as(C.c_void_p),
+                                                          len(iq), payload.ctypes.data_as(C.c_void_p),
+                                                          res.ctypes.data_as(C.c_void_p), pk.ctypes.data_as(C.c_void_p),
+                                                          C.byref(n)))
+        k = n.value
+        return [bytes(payload[i, :max(int(res[i]["n_bytes"]), 0)]) for i in range(k)], res[:k], pk[:k]
 
     def awgn_batch(self, iq, snr_db, seed=0):
         n, count = iq.shape

@@ -118,3 +118,24 @@ def test_full_chain_loopback_through_the_air(env):
                 assert bits(out[p, 0, :19]) == bits(pay[p].cpu().numpy())
                 ok += 1
         assert ok >= 20, (sf, ok)
+
+
+def test_host_call_and_cli_on_the_golden_capture(env, tmp_path):
+    """lora_b200_std_receive_stream_host with mtu = 0 (frame length taken from the headers) and the CLI over it."""
+    import subprocess
+    L = env["L"]
+    iq = np.load(os.path.join(HERE, "golden", "capture_sf7.npz"))["iq"]
+    frames, res, pk = L.Context(7, osr=2).std_receive_stream_host(L.std_cfg(7), iq)
+    assert frames == [f"hello world: {k}".encode() for k in range(16)]
+    assert (res["crc_ok"] == 1).all() and (res["symbols_used"] == 33).all()
+    assert [int(s) for s in pk["start"]] == [1568 + 8352 * k for k in range(16)]
+    exe = os.path.join(os.path.dirname(HERE), "lora-sdr-lightweight-standalone-library-_b200", "bin", "lora_rx_stream")
+    path = tmp_path / "capture.bin"
+    np.ascontiguousarray(iq).tofile(path)
+    out = subprocess.run([exe, f"--in={path}", "--sf=7", "--osr=2"], capture_output=True, text=True, check=True).stdout
+    lines = out.strip().split("\n")
+    assert lines[0] == "Frames: 16"
+    for k in range(16):
+        text = f"hello world: {k}"
+        assert lines[1 + k] == (f"Frame {k} @{1568 + 8352 * k}: len {len(text)} CR 4/5 CRC ok Payload: "
+                                f"{text.encode().hex()}  \"{text}\"")
