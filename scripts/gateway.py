@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--sf12-packets", type=int, default=4, help="packets in an SF12 channel; other SFs match its sample count")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--graph", action="store_true", help="capture one step (all launches + the gather) in a CUDA graph")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -88,7 +89,7 @@ def main():
     rec = torch.zeros((n_max, REC), dtype=torch.uint8, device="cuda")
     gathered = torch.zeros((world * n_max, REC), dtype=torch.uint8, device="cuda") if dist is not None else rec
 
-    def step():
+    def compute():
         at = 0
         for i in items:
             i["ctx"].demod_batch(i["iq"], mode=L.DEMOD_LEGACY_DECHIRP, symbols=i["rx"], metrics=i["met"])
@@ -99,19 +100,42 @@ def main():
             rows[:, 32:ID_AT] = i["out"][:, :ID_AT - 32]
             rows[:, ID_AT:REC] = i["ident"]
             at += i["n"]
+
+    def gather():
         if dist is not None:  # the only NVLink traffic of a step
             dist.all_gather_into_tensor(gathered, rec)
+
+    def step():
+        compute()
+        gather()
 
     for _ in range(max(args.warmup, 3)):
         step()
     torch.cuda.synchronize()
+    run = step
+    graphed = False
+    if args.graph:
+        # A step at N = 8 is ~70 launches for ~0.8 ms of kernel time: launch-bound.  After the warm-up nothing inside
+        # the library allocates or synchronises, so the local part of the step -- the library's launches on torch's
+        # current stream and the record assembly -- is captured once and replayed.  The NCCL all-gather stays outside
+        # the graph: capturing it made the 8-rank run hang (measured once, 600 s), and it is one launch.
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            compute()
+
+        def run():
+            g.replay()
+            gather()
+        graphed = True
+        run()
+        torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        step()
+        run()
     e1.record()
     torch.cuda.synchronize()
     if dist is not None:
@@ -159,7 +183,7 @@ def main():
                        "packets_per_channel": {str(sf): k_of[sf] for sf in SFS}, "samples": total_samples,
                        "packets": sum(all_counts), "record_bytes": REC,
                        "gather_bytes_per_step": world * n_max * REC if world > 1 else 0,
-                       "load_spread": (max(load) - min(load)) / max(load)},
+                       "load_spread": (max(load) - min(load)) / max(load), "cuda_graph": graphed},
             "crc_ok_packets": int(tot[0].item()), "crc_ok_but_payload_damaged": int(tot[3].item()),
             "crc_ok_at_snr_ge_0dB": int(tot[2].item()) / max(int(tot[1].item()), 1)}))
     if dist is not None:
