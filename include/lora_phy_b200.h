@@ -250,6 +250,10 @@ typedef struct lora_b200_stream_cfg {
     uint32_t mtu;          /* LoRaDemod::setMTU, default 256 */
     uint32_t max_packets;  /* capacity of d_packets per stream */
     uint32_t max_symbols;  /* capacity of d_symbols per stream */
+    uint32_t frame_header; /* 0 = as LoRaDemod: data symbols until mtu or a squelched window (:286-310).  Not in the
+                              reference: 1 = after eight data symbols read the deployed chain's explicit header and stop
+                              at the frame length it announces (capped by mtu; an invalid header ends the frame at
+                              eight symbols); 2 = the same for frames sent with low-data-rate optimisation */
 } lora_b200_stream_cfg;
 
 typedef struct lora_b200_stream_packet {
@@ -301,9 +305,8 @@ int lora_b200_std_stream_decode_batch(lora_b200_ctx* ctx, const lora_b200_std_cf
                                       lora_b200_std_result* d_std_results, void* stream);
 /* One capture, host buffers in and out: copy in, frame synchroniser (decimating by the context's osr), deployed chain,
  * copy out.  h_payload: cfg->max_packets x LORA_B200_PAYLOAD_STRIDE bytes; h_results: cfg->max_packets; h_packets
- * (optional): cfg->max_packets records; *n_packets: packets stored.  stream_cfg->mtu = 0 takes the frame length from
- * the capture: a first pass stops after every header block, the second collects the longest frame a valid header
- * announced (frames shorter than that must be followed by at least the difference of silence).
+ * (optional): cfg->max_packets records; *n_packets: packets stored.  stream_cfg->mtu = 0 takes every frame's length
+ * from its own header (frame_header mode of the synchroniser; implicit-header frames use cfg->payload_len).
  * bin/lora_rx_stream is this call behind a CLI. */
 int lora_b200_std_receive_stream_host(lora_b200_ctx* ctx, const lora_b200_std_cfg* cfg,
                                       const lora_b200_stream_cfg* stream_cfg, const lora_b200_c32* h_iq, size_t count,

@@ -1005,6 +1005,7 @@ static int stream_detect_locked(lora_b200_ctx* c, const lora_b200_stream_cfg* cf
     a.thresh = cfg->thresh_db;
     a.mtu = cfg->mtu;
     a.sync = cfg->sync;
+    a.frame_header = static_cast<int>(cfg->frame_header);
     a.symbols = d_symbols;
     a.sym_cap = cfg->max_symbols;
     a.packets = reinterpret_cast<StreamPacket*>(d_packets);
@@ -1068,28 +1069,15 @@ extern "C" int lora_b200_std_receive_stream_host(lora_b200_ctx* c, const lora_b2
                     c->s_results.as<lora_b200_std_result>(), static_cast<int>(np), d_pk, d_res, cfg->max_packets};
     if (sc.mtu == 0) {
         // The synchroniser (LoRaDemod.cpp:286-310) collects data symbols until `mtu` or a squelched window; it does not
-        // read the header.  mtu = 0 asks for the frame length to be taken from the capture itself: a first pass that
-        // stops after every header block, then the longest frame any valid header announces.
+        // read the header.  mtu = 0 asks for every frame's own length: implicit-header frames have a known one, explicit
+        // headers are read by the synchroniser itself after the eighth data symbol (frame_header mode).
         if (g->implicit_header) {
             sc.mtu = static_cast<uint32_t>(std_symbol_count(*g, g->payload_len));
         } else {
-            sc.mtu = 8;
-            if (int rc = stream_detect_locked(c, &sc, c->s_iq.as<lora_b200_c32>(), 1, count, count, c->s_sym.as<int16_t>(),
-                                              d_pk, d_res, st))
-                return rc;
-            CU(launch_std_decode(a, st));
-            CU(cudaMemcpyAsync(h_results, c->s_results.p, sizeof(lora_b200_std_result) * np, cudaMemcpyDeviceToHost, st));
-            CU(cudaStreamSynchronize(st));
-            size_t longest = 0;
-            for (size_t k = 0; k < np; ++k) {
-                const lora_b200_std_result& r = h_results[k];
-                if (r.n_bytes != -3 || !r.hdr_ok) continue; // -3: header valid, frame cut short by mtu
-                lora_b200_std_cfg f = *g;
-                f.cr = r.hdr_cr; f.has_crc = r.has_crc;
-                longest = std::max(longest, std_symbol_count(f, r.hdr_length));
-            }
-            if (longest == 0) return LORA_B200_OK; // no frame with a valid header
-            sc.mtu = static_cast<uint32_t>(longest);
+            lora_b200_std_cfg longest = *g;
+            longest.cr = 4; longest.has_crc = 1;
+            sc.mtu = static_cast<uint32_t>(std_symbol_count(longest, 255));
+            sc.frame_header = g->ldro ? 2u : 1u;
         }
     }
     if (int rc = stream_detect_locked(c, &sc, c->s_iq.as<lora_b200_c32>(), 1, count, count, c->s_sym.as<int16_t>(), d_pk,

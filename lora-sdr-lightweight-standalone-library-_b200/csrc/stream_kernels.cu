@@ -8,6 +8,8 @@
 // Every thread of a slot runs the state machine on identical inputs, so no decision needs broadcasting.
 #include "stream_kernels.h"
 
+#include "std_chain.cuh"
+
 #include <cmath>
 
 #include "demod_kernels.h" // g_launches
@@ -266,7 +268,8 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
         float fine_err = 0.0f;
         short prev_value = 0;
         size_t pos = 0, cur_start = 0;
-        unsigned sym_count = 0, n_pkt = 0;
+        unsigned sym_count = 0, n_pkt = 0, frame_limit = a.mtu;
+        unsigned long long hdr_lo = 0, hdr_hi = 0;
         size_t sym_used = 0;
 
         const size_t avail = (a.count + a.osr - 1) / a.osr; // samples 0, osr, 2*osr, ... of the stream
@@ -318,13 +321,26 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
                 total = (size_t)(N / 4) + (size_t)(long long)(freq_err / 2); // size_t + int, modulo 2^64 like the reference
                 fine_err = __fadd_rn(fine_err, (float)(freq_err / 2));
                 sym_count = 0;
+                hdr_lo = hdr_hi = 0;
+                frame_limit = a.mtu;
                 cur_start = pos + total;
             } break;
             default: { // DATASYMBOLS, :289-310
                 total = N;
                 if (t == 0 && sym_used + sym_count < a.sym_cap) out[sym_used + sym_count] = (int16_t)value;
+                if (a.frame_header && sym_count < 8) { // keep the header block: four 16-bit symbols per word
+                    const unsigned long long v16 = (unsigned long long)(value & 0xffffu) << (16 * (sym_count & 3));
+                    if (sym_count < 4) hdr_lo |= v16; else hdr_hi |= v16;
+                }
                 ++sym_count;
-                if (sym_count >= a.mtu || squelched) {
+                if (a.frame_header && sym_count == 8) { // not in the reference: frame length from the explicit header
+                    uint16_t hs[8];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { hs[k] = (uint16_t)(hdr_lo >> (16 * k)); hs[4 + k] = (uint16_t)(hdr_hi >> (16 * k)); }
+                    const unsigned want = stdchain::std_frame_symbols(SF, a.frame_header == 2, hs);
+                    frame_limit = want ? min(want, a.mtu) : 8u; // an invalid header ends the frame here
+                }
+                if (sym_count >= frame_limit || squelched) {
                     if (t == 0 && n_pkt < a.pkt_cap) {
                         StreamPacket p;
                         p.start = cur_start;

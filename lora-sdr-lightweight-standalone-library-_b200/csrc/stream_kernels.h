@@ -40,6 +40,8 @@ struct StreamDetectArgs {
     const c64* fine;  // N * 128 (LoRaDemod.cpp:110-117)
     float power_scale, thresh;
     unsigned mtu, sync;
+    int frame_header; // 0: symbols until mtu or squelch (LoRaDemod.cpp:286-310); 1 / 2: after eight data symbols read the
+                      // deployed chain's explicit header (2 = LDRO) and stop at the frame length it announces
     int16_t* symbols;
     size_t sym_cap;
     StreamPacket* packets;

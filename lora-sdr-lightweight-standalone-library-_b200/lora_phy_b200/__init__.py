@@ -52,7 +52,7 @@ assert PKT_METRICS.itemsize == 16 and CHAIN_RESULT.itemsize == 16 and STD_RESULT
 
 class StreamCfg(C.Structure):  # lora_b200_stream_cfg
     _fields_ = [("sync", C.c_uint8), ("thresh_db", C.c_float), ("mtu", C.c_uint32), ("max_packets", C.c_uint32),
-                ("max_symbols", C.c_uint32)]
+                ("max_symbols", C.c_uint32), ("frame_header", C.c_uint32)]
 
 
 # lora_b200_stream_packet / lora_b200_stream_result as numpy record layouts
@@ -315,7 +315,8 @@ class Context:
                                                        padding, _ptr(out), out.stride(0), _stream()))
         return out
 
-    def stream_detect_batch(self, iq, sync=0x12, thresh_db=-30.0, mtu=256, max_packets=8, max_symbols=1024):
+    def stream_detect_batch(self, iq, sync=0x12, thresh_db=-30.0, mtu=256, max_packets=8, max_symbols=1024,
+                            frame_header=0):
         """LoRaDemod::work over every row of `iq` (streams x samples).  -> (symbols int16 [streams, max_symbols],
         packets uint8 [streams, max_packets, 24] (view with STREAM_PACKET), results uint8 [streams, 16] (STREAM_RESULT))."""
         import torch
@@ -323,7 +324,7 @@ class Context:
         sym = torch.zeros((n, max_symbols), dtype=torch.int16, device=iq.device)
         pk = torch.zeros((n, max_packets, STREAM_PACKET.itemsize), dtype=torch.uint8, device=iq.device)
         res = torch.zeros((n, STREAM_RESULT.itemsize), dtype=torch.uint8, device=iq.device)
-        cfg = StreamCfg(sync, thresh_db, mtu, max_packets, max_symbols)
+        cfg = StreamCfg(sync, thresh_db, mtu, max_packets, max_symbols, frame_header)
         stride = iq.stride(0) if n > 1 else max(iq.stride(0), count)  # a size-1 dimension may report any stride
         _check(self.lib.lora_b200_stream_detect_batch(self.h, C.byref(cfg), _ptr(iq), n, count, stride, _ptr(sym),
                                                       _ptr(pk), _ptr(res), _stream()))

@@ -160,6 +160,7 @@ uint8_t  orc_std_header_checksum(unsigned n0, unsigned n1, unsigned n2);
 void     orc_std_whitening(uint8_t* seq, size_t n);
 uint16_t orc_std_crc(const uint8_t* payload, size_t len);
 size_t   orc_std_symbol_count(const orc_std_cfg* c, size_t len);
+size_t   orc_std_frame_symbols(unsigned sf, int ldro, const uint16_t* sym);
 size_t   orc_std_encode(const orc_std_cfg* c, const uint8_t* payload, size_t len, uint16_t* out, size_t cap);
 long     orc_std_decode(const orc_std_cfg* c, const uint16_t* symbols, size_t nsym, uint8_t* out, size_t cap,
                         orc_std_info* info);
@@ -174,5 +175,11 @@ void   orc_stream_tables(unsigned sf, orc_c32* up, orc_c32* down, orc_c32* fine)
 size_t orc_stream_demod(unsigned sf, unsigned char sync, float thresh, size_t mtu, const orc_c32* samples,
                         size_t count, int16_t* out_symbols, size_t sym_cap, uint32_t* pkt_len, uint64_t* pkt_start,
                         int32_t* pkt_err, size_t pkt_cap, uint64_t* consumed);
+/* The same state machine with one addition that is NOT in the reference: frame_header = 1 (2 with LDRO) reads the
+ * deployed chain's explicit header after eight data symbols and ends the frame at the length it announces (capped by
+ * mtu; an invalid header ends it at eight symbols).  frame_header = 0 is orc_stream_demod. */
+size_t orc_stream_demod_hdr(unsigned sf, unsigned char sync, float thresh, size_t mtu, int frame_header,
+                            const orc_c32* samples, size_t count, int16_t* out_symbols, size_t sym_cap, uint32_t* pkt_len,
+                            uint64_t* pkt_start, int32_t* pkt_err, size_t pkt_cap, uint64_t* consumed);
 
 #endif

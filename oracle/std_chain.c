@@ -158,6 +158,23 @@ static void std_deinterleave(const uint16_t* sym, unsigned n_cw, unsigned cw_len
     }
 }
 
+/* Symbols in the frame whose explicit header sits in the eight reduced-rate symbols `sym`; 0 when the header checksum
+ * fails, the coding rate is not 1..4 or the length is zero. */
+size_t orc_std_frame_symbols(unsigned sf, int ldro, const uint16_t* sym)
+{
+    unsigned cw[12];
+    int fixed = 0, bad = 0;
+    unsigned nib[5];
+    if (sf < 7 || sf > 12) return 0;
+    std_deinterleave(sym, sf - 2, 8, sf, 1, cw);
+    for (unsigned k = 0; k < 5; ++k) nib[k] = std_hamming_decode(cw[k], 4, &fixed, &bad);
+    const unsigned len = nib[0] << 4 | nib[1], cr = nib[2] >> 1;
+    const unsigned chk = (nib[3] & 1u) << 4 | nib[4];
+    if (chk != orc_std_header_checksum(nib[0], nib[1], nib[2]) || cr < 1 || cr > 4 || len == 0) return 0;
+    orc_std_cfg c = {sf, cr, ldro, 0, (int)(nib[2] & 1u), 0};
+    return orc_std_symbol_count(&c, len);
+}
+
 size_t orc_std_encode(const orc_std_cfg* c, const uint8_t* payload, size_t len, uint16_t* out, size_t cap)
 {
     const size_t nsym = orc_std_symbol_count(c, len);

@@ -106,6 +106,14 @@ size_t orc_stream_demod(unsigned sf, unsigned char sync, float thresh, size_t mt
                         int16_t* out_symbols, size_t sym_cap, uint32_t* pkt_len, uint64_t* pkt_start, int32_t* pkt_err,
                         size_t pkt_cap, uint64_t* consumed)
 {
+    return orc_stream_demod_hdr(sf, sync, thresh, mtu, 0, samples, count, out_symbols, sym_cap, pkt_len, pkt_start, pkt_err,
+                                pkt_cap, consumed);
+}
+
+size_t orc_stream_demod_hdr(unsigned sf, unsigned char sync, float thresh, size_t mtu, int frame_header,
+                            const orc_c32* samples, size_t count, int16_t* out_symbols, size_t sym_cap, uint32_t* pkt_len,
+                            uint64_t* pkt_start, int32_t* pkt_err, size_t pkt_cap, uint64_t* consumed)
+{
     enum { FRAMESYNC, DOWNCHIRP0, DOWNCHIRP1, QUARTERCHIRP, DATASYMBOLS };
     const size_t N = (size_t)1 << sf;
     orc_c32* tw = malloc(sizeof(orc_c32) * N);
@@ -123,7 +131,8 @@ size_t orc_stream_demod(unsigned sf, unsigned char sync, float thresh, size_t mt
     float fine_err = 0.0f;                 /* _finefreqError: see the note on prev_value */
     short prev_value = 0;                  /* _prevValue, _freqError, _finefreqError are left uninitialised by the
                                               reference's constructor (:68-75); zero is assumed here */
-    size_t sym_count = 0, n_pkt = 0, sym_used = 0, pos = 0;
+    size_t sym_count = 0, n_pkt = 0, sym_used = 0, pos = 0, frame_limit = mtu;
+    uint16_t hdr_sym[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint64_t cur_start = 0;
 
     while (pos + 2 * N <= count) {         /* :148 */
@@ -178,13 +187,19 @@ size_t orc_stream_demod(unsigned sf, unsigned char sync, float thresh, size_t mt
             total = N / 4 + (size_t)(freq_err / 2); /* size_t + int: wraps modulo 2^64 exactly as the reference does */
             fine_err += (float)(freq_err / 2);
             sym_count = 0;
+            frame_limit = mtu;
             cur_start = pos + total;
         } break;
         case DATASYMBOLS: {                 /* :289-310 */
             total = N;
             if (sym_used + sym_count < sym_cap) out_symbols[sym_used + sym_count] = (int16_t)value;
+            if (frame_header && sym_count < 8) hdr_sym[sym_count] = (uint16_t)value;
             ++sym_count;
-            if (sym_count >= mtu || squelched) {
+            if (frame_header && sym_count == 8) { /* not in the reference: frame length from the explicit header */
+                const size_t want = orc_std_frame_symbols(sf, frame_header == 2, hdr_sym);
+                frame_limit = want ? (want < mtu ? want : mtu) : 8;
+            }
+            if (sym_count >= frame_limit || squelched) {
                 if (n_pkt < pkt_cap) {
                     pkt_len[n_pkt] = (uint32_t)sym_count;
                     pkt_start[n_pkt] = cur_start;

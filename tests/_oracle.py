@@ -275,16 +275,16 @@ class Lib:
         self.fn("stream_tables", None, [C.c_uint, c64p, c64p, c64p])(sf, up, down, fine)
         return up, down, fine
 
-    def stream_demod(self, sf, samples, sync=0x12, thresh=-30.0, mtu=256, pkt_cap=64):
+    def stream_demod(self, sf, samples, sync=0x12, thresh=-30.0, mtu=256, pkt_cap=64, frame_header=0):
         """-> (list of int16 symbol arrays, starts, freq errors, samples consumed)"""
         samples = np.ascontiguousarray(samples, np.complex64)
         sym = np.zeros(pkt_cap * mtu, np.int16)
         plen, pstart, perr = np.zeros(pkt_cap, np.uint32), np.zeros(pkt_cap, np.uint64), np.zeros(pkt_cap, np.int32)
         consumed = C.c_uint64()
-        n = self.fn("stream_demod", C.c_size_t, [C.c_uint, C.c_ubyte, C.c_float, C.c_size_t, c64p, C.c_size_t,
+        n = self.fn("stream_demod_hdr", C.c_size_t, [C.c_uint, C.c_ubyte, C.c_float, C.c_size_t, C.c_int, c64p, C.c_size_t,
                                                  C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
                                                  C.c_size_t, C.POINTER(C.c_uint64)])(
-            sf, sync, thresh, mtu, samples, len(samples), sym.ctypes.data, len(sym), plen.ctypes.data,
+            sf, sync, thresh, mtu, frame_header, samples, len(samples), sym.ctypes.data, len(sym), plen.ctypes.data,
             pstart.ctypes.data, perr.ctypes.data, pkt_cap, C.byref(consumed))
         n = min(n, pkt_cap)
         pk, o = [], 0

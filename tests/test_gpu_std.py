@@ -139,3 +139,47 @@ def test_host_call_and_cli_on_the_golden_capture(env, tmp_path):
         text = f"hello world: {k}"
         assert lines[1 + k] == (f"Frame {k} @{1568 + 8352 * k}: len {len(text)} CR 4/5 CRC ok Payload: "
                                 f"{text.encode().hex()}  \"{text}\"")
+
+
+def test_frame_header_mode_equals_oracle(env):
+    """lora_b200_stream_cfg.frame_header: the synchroniser reads the frame length from the explicit header after eight
+    data symbols.  Same packets, symbols and consumed-sample counts as the oracle's state machine, on a train of unequal
+    frames one padding symbol apart (with noise) and on the golden capture."""
+    torch, L, ORC, orc_cfg = env["torch"], env["L"], env["ORC"], env["orc_cfg"]
+    rng = np.random.default_rng(11)
+    for sf, cr, ldro in ((8, 2, False), (9, 4, True), (7, 1, False)):
+        pays = [rng.integers(0, 256, n, dtype=np.uint8) for n in (3, 60, 1, 17, 200)]
+        syms = [ORC.std_encode(orc_cfg(sf, cr, ldro), p) for p in pays]
+        rows = []
+        for r in range(3):
+            order = rng.permutation(len(syms))
+            x = np.concatenate([ORC.frame_modulate(sf, syms[k], padding=1, ampl=0.5) for k in order] +
+                               [np.zeros(3 << sf, np.complex64)])
+            x = x + ((rng.standard_normal(len(x)) + 1j * rng.standard_normal(len(x))) * 0.02).astype(np.complex64)
+            rows.append((order, x.astype(np.complex64)))
+        n = max(len(x) for _, x in rows)
+        batch = np.zeros((3, n), np.complex64)
+        for r, (_, x) in enumerate(rows):
+            batch[r, :len(x)] = x
+        ctx = L.Context(sf)
+        mode = 2 if ldro else 1
+        sym, pk, res = ctx.stream_detect_batch(torch.from_numpy(batch).cuda(), mtu=1000, max_packets=8, max_symbols=2048,
+                                               frame_header=mode)
+        out, sr = ctx.std_stream_decode_batch(L.std_cfg(sf, cr, ldro), sym, pk, res)
+        pkr, rr = L.stream_records(pk, res)
+        sym, out = sym.cpu().numpy(), out.cpu().numpy()
+        sr = sr.cpu().numpy().reshape(3, 8, 16).view(L.STD_RESULT).reshape(3, 8)
+        for r, (order, _) in enumerate(rows):
+            want, start, err, consumed = ORC.stream_demod(sf, batch[r], mtu=1000, pkt_cap=8, frame_header=mode)
+            assert int(rr[r]["n_packets"]) == len(want) == len(order) and int(rr[r]["consumed"]) == consumed
+            for k, w in enumerate(want):
+                a = int(pkr[r, k]["first_symbol"])
+                assert int(pkr[r, k]["n_symbols"]) == len(w) == len(syms[order[k]]) and int(pkr[r, k]["start"]) == int(start[k])
+                assert bits(sym[r, a:a + len(w)]) == bits(w)
+                p = pays[order[k]]
+                assert int(sr[r, k]["n_bytes"]) == len(p) and sr[r, k]["crc_ok"] == 1 and bits(out[r, k, :len(p)]) == bits(p)
+    iq = np.load(os.path.join(HERE, "golden", "capture_sf7.npz"))["iq"]
+    sym, pk, res = L.Context(7, osr=2).stream_detect_batch(torch.from_numpy(np.ascontiguousarray(iq)[None]).cuda(), mtu=600,
+                                                           max_packets=32, max_symbols=2048, frame_header=1)
+    pkr, rr = L.stream_records(pk, res)
+    assert int(rr[0]["n_packets"]) == 16 and (pkr[0, :16]["n_symbols"] == 33).all()

@@ -100,3 +100,26 @@ def test_rejections():
         rejected += ret == -1
         assert ret == -1 or info.corrected or info.uncorrectable       # never silently accepted
     assert rejected > 0
+
+
+def test_synchroniser_reads_the_frame_length_from_the_header():
+    """frame_header mode (not in the reference): no per-capture mtu is needed, and frames of different lengths that follow
+    each other closely are each cut at their own last symbol."""
+    x = np.ascontiguousarray(capture()[0::2])
+    frames, start, _, _ = ORC.stream_demod(7, x, mtu=600, pkt_cap=32, frame_header=1)
+    assert len(frames) == 16 and all(len(f) == 33 for f in frames)
+    assert [int(s) for s in start] == [1568 + 8352 * k for k in range(16)]
+    # a train of unequal frames, one symbol of padding between them
+    sf, cfg = 8, std_cfg(8, cr=2)
+    rng = np.random.default_rng(3)
+    pays = [rng.integers(0, 256, n, dtype=np.uint8) for n in (3, 60, 1, 17, 200)]
+    syms = [ORC.std_encode(cfg, p) for p in pays]
+    x = np.concatenate([ORC.frame_modulate(sf, s, padding=1, ampl=0.5) for s in syms] + [np.zeros(3 << sf, np.complex64)])
+    frames, _, _, _ = ORC.stream_demod(sf, x, mtu=1000, pkt_cap=16, frame_header=1)
+    assert [len(f) for f in frames] == [len(s) for s in syms]
+    for f, p in zip(frames, pays):
+        ret, data, info = ORC.std_decode(std_cfg(sf), f.astype(np.uint16) & 255)
+        assert ret == len(p) and bytes(data) == bytes(p) and info.crc_ok == 1
+    # the reference's behaviour (frame_header = 0) swallows the following frames into the first packet
+    frames0, _, _, _ = ORC.stream_demod(sf, x, mtu=1000, pkt_cap=16)
+    assert len(frames0) < len(syms)
