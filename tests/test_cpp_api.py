@@ -58,6 +58,22 @@ def test_runners_fail_loudly_without_a_gpu(tmp_path):
     assert r.returncode != 0
 
 
+def test_stream_receiver_cli_fails_loudly_without_a_gpu(tmp_path):
+    """bin/lora_rx_stream is built everywhere (it needs no reference source); with no device it must say so and
+    print no frames -- there is no CPU path behind it."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("this check is for the CPU-only container")
+    exe = os.path.join(os.path.dirname(RX), "lora_rx_stream")
+    assert os.path.exists(exe), "bin/lora_rx_stream was not built"
+    f = tmp_path / "z.iq"
+    np.zeros(4096, np.complex64).tofile(f)
+    r = subprocess.run([exe, f"--in={f}", "--sf=7"], capture_output=True, text=True)
+    assert r.returncode != 0 and "Frames" not in r.stdout and "no CUDA device" in r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode != 0 and "Usage" in r.stderr
+
+
 needs_runners = pytest.mark.skipif(not os.path.exists(RX), reason="bin/rx_runner not built (no reference tree at build time)")
 
 
