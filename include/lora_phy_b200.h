@@ -235,6 +235,11 @@ int lora_b200_receive_host_i16(lora_b200_ctx* ctx, int mode, const lora_b200_cha
                                const int16_t* h_iq, size_t n_packets, size_t samples_per_packet, float scale,
                                uint8_t* h_payload, lora_b200_chain_result* h_results,
                                lora_b200_pkt_metrics* h_metrics);
+/* The same for interleaved int8 I/Q (RTL-SDR class front ends): a quarter of the PCIe bytes of the float call. */
+int lora_b200_receive_host_i8(lora_b200_ctx* ctx, int mode, const lora_b200_chain_cfg* cfg,
+                              const int8_t* h_iq, size_t n_packets, size_t samples_per_packet, float scale,
+                              uint8_t* h_payload, lora_b200_chain_result* h_results,
+                              lora_b200_pkt_metrics* h_metrics);
 
 /* ---- continuous-stream front end and full frames (upstream Pothos blocks) --------------------------------------
  * LoRaDemod::work (LoRa-SDR/LoRaDemod.cpp:145-327): the frame synchroniser state machine -- 10-chirp preamble with

@@ -868,6 +868,25 @@ extern "C" int lora_b200_receive_host_i16(lora_b200_ctx* c, int mode, const lora
     return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
 }
 
+extern "C" int lora_b200_receive_host_i8(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
+                                         const int8_t* h_iq, size_t n_packets, size_t count, float scale,
+                                         uint8_t* h_payload, lora_b200_chain_result* h_results,
+                                         lora_b200_pkt_metrics* h_metrics)
+{
+    if (!c || !h_iq || !h_payload || !h_results) return fail(LORA_B200_EINVAL, "null argument");
+    if (n_packets == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    if (count / (static_cast<size_t>(c->n) * c->cfg.osr) < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
+    const size_t samples = count * n_packets;
+    CU(c->s_iq.reserve(sizeof(float2) * samples));
+    CU(c->s_raw.reserve(sizeof(char2) * samples));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(c->s_raw.p, h_iq, sizeof(char2) * samples, cudaMemcpyHostToDevice, st));
+    CU(launch_convert_i8(c->s_raw.as<char2>(), c->s_iq.as<float2>(), samples, scale, c->sm_count, st));
+    return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
+}
+
 // ---- small host-buffer entry points used by include/lora_phy/phy.hpp -------------------------------------------
 extern "C" int lora_b200_encode_host(lora_b200_ctx* c, const uint8_t* h_bytes, size_t n_bytes, uint16_t* h_symbols,
                                      size_t symbol_cap, size_t* produced)

@@ -416,4 +416,41 @@ cudaError_t launch_convert_i16(const short2* in, float2* out, size_t n, float sc
     return cudaGetLastError();
 }
 
+// int8 I/Q (RTL-SDR class front ends, or a gateway that trades resolution for link bytes): 2 bytes per sample over PCIe.
+// The conversion is exact (an 8-bit integer is a float; one rounding in the multiply), so the results equal the float
+// path run on the converted samples.
+__global__ void __launch_bounds__(256) convert_i8_kernel(const char2* __restrict__ in, float2* __restrict__ out, size_t n, float scale)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t n8 = ((reinterpret_cast<uintptr_t>(in) & 15u) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) ? n / 8 : 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) { // 8 samples: 16 bytes in, 64 out
+        const int4 v = __ldg(reinterpret_cast<const int4*>(in) + i);
+        const int w[4] = {v.x, v.y, v.z, v.w};
+        float4 o[4];
+        float* f = reinterpret_cast<float*>(o);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) f[4 * k + b] = __fmul_rn((float)(signed char)((w[k] >> (8 * b)) & 0xff), scale);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) reinterpret_cast<float4*>(out)[4 * i + k] = o[k];
+    }
+    for (size_t i = 8 * n8 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const char2 v = in[i];
+        out[i] = make_float2(__fmul_rn((float)v.x, scale), __fmul_rn((float)v.y, scale));
+    }
+}
+
+cudaError_t launch_convert_i8(const char2* in, float2* out, size_t n, float scale, int sm_count, cudaStream_t st)
+{
+    size_t blocks = (n / 8 + 255) / 256;
+    const size_t cap = (size_t)sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    convert_i8_kernel<<<(unsigned)blocks, 256, 0, st>>>(in, out, n, scale);
+    ++g_launches;
+    return cudaGetLastError();
+}
+
 } // namespace lora_b200

@@ -77,5 +77,6 @@ extern unsigned long long g_launches; // kernels launched by this library (bench
 
 // SDR sample ingest: interleaved int16 (I, Q) -> float32 * scale.  With scale = 2^-15 the conversion is exact.
 cudaError_t launch_convert_i16(const short2* in, float2* out, size_t n, float scale, int sm_count, cudaStream_t st);
+cudaError_t launch_convert_i8(const char2* in, float2* out, size_t n, float scale, int sm_count, cudaStream_t st);
 
 } // namespace lora_b200

@@ -128,6 +128,8 @@ _SIGNATURES = {
                                          C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lora_b200_receive_host_i16": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
                                              C.c_size_t, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_receive_host_i8": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
+                                            C.c_size_t, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lora_b200_frame_samples": (C.c_size_t, [C.c_void_p, C.c_size_t, C.c_uint]),
     "lora_b200_frame_modulate_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float,
                                                  C.c_uint8, C.c_uint, C.c_void_p, C.c_size_t, C.c_void_p]),
@@ -491,6 +493,20 @@ class Context:
         _check(self.lib.lora_b200_receive_host_i16(self.h, mode, C.byref(cfg), iq_i16.ctypes.data_as(C.c_void_p), n, count,
                                                    scale, payload.ctypes.data_as(C.c_void_p),
                                                    results.ctypes.data_as(C.c_void_p), metrics.ctypes.data_as(C.c_void_p)))
+        return payload, results, metrics
+
+
+    def receive_host_i8(self, cfg, iq_i8, scale=1.0 / 128.0, mode=DEMOD_LEGACY_DECHIRP, payload=None, results=None,
+                        metrics=None):
+        """Host int8 IQ [n, samples, 2] (I, Q interleaved) -> the same outputs as receive_host on float32(iq) * scale."""
+        iq_i8 = np.ascontiguousarray(iq_i8, np.int8)
+        n, count = iq_i8.shape[0], iq_i8.shape[1]
+        payload = np.zeros((n, PAYLOAD_STRIDE), np.uint8) if payload is None else payload
+        results = np.zeros(n, CHAIN_RESULT) if results is None else results
+        metrics = np.zeros(n, PKT_METRICS) if metrics is None else metrics
+        _check(self.lib.lora_b200_receive_host_i8(self.h, mode, C.byref(cfg), iq_i8.ctypes.data_as(C.c_void_p), n, count,
+                                                  scale, payload.ctypes.data_as(C.c_void_p),
+                                                  results.ctypes.data_as(C.c_void_p), metrics.ctypes.data_as(C.c_void_p)))
         return payload, results, metrics
 
 

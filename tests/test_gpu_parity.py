@@ -391,6 +391,35 @@ def test_int16_ingest_equals_float_path(env):
         assert (r1["crc_ok"] == 1).all() and bytes(p1[:, :16]) == bytes(pay.cpu().numpy())
 
 
+def test_int8_ingest_equals_float_path(env):
+    """lora_b200_receive_host_i8: int8 I/Q (a quarter of the PCIe bytes) converted exactly on the device; results equal
+    the float call on the converted samples, ragged (non multiple of eight) sample counts included."""
+    torch, L = env["torch"], env["L"]
+    for sf, amp in ((7, 0.5), (9, 0.4)):
+        ctx = L.Context(sf)
+        cfg = L.chain_cfg(sf, 1)
+        gen = torch.Generator(device="cuda").manual_seed(40 + sf)
+        pay = torch.randint(0, 256, (21, 16), dtype=torch.uint8, device="cuda", generator=gen)
+        iq = ctx.modulate_batch(ctx.chain_encode_batch(cfg, pay), amplitude=amp)
+        ctx.awgn_batch(iq, torch.full((21,), 25.0, device="cuda"), seed=sf)
+        h = iq.cpu().numpy()
+        q = np.clip(np.round(np.stack([h.real, h.imag], axis=-1) * 96.0), -128, 127).astype(np.int8)
+        as_float = q.astype(np.float32) * np.float32(1.0 / 128.0)
+        as_float = (as_float[..., 0] + 1j * as_float[..., 1]).astype(np.complex64)
+        p1, r1, m1 = ctx.receive_host_i8(cfg, q)
+        p2, r2, m2 = ctx.receive_host(cfg, as_float)
+        assert bits(p1) == bits(p2) and bits(r1) == bits(r2) and bits(m1) == bits(m2)
+        assert (r1["crc_ok"] == 1).all() and bytes(p1[:, :16]) == bytes(pay.cpu().numpy())
+    # a lone ragged buffer: the tail path of the converter
+    ctx = L.Context(7)
+    rng = np.random.default_rng(1)
+    q = rng.integers(-128, 128, (1, 3 * 128, 2), dtype=np.int8)
+    f = (q[..., 0].astype(np.float32) + 1j * q[..., 1].astype(np.float32)).astype(np.complex64) * np.float32(1 / 128.0)
+    a = ctx.receive_host_i8(L.chain_cfg(7, 1), q[:, :381], mode=L.DEMOD_LEGACY)   # this entry point takes ragged tails
+    b = ctx.receive_host(L.chain_cfg(7, 1), np.ascontiguousarray(f[:, :381]), mode=L.DEMOD_LEGACY)
+    assert all(bits(x) == bits(y) for x, y in zip(a, b))
+
+
 def test_stream_pipelined_sub_batches_give_the_same_results(env):
     """lora_b200_set_overlap: scan+estimate of sub-batch k+1 on a second stream beside the demod of sub-batch k (only
     taken for batches of 256 MB and more).  Off by default because it is no faster; it must still be exact."""
