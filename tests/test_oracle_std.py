@@ -123,3 +123,25 @@ def test_synchroniser_reads_the_frame_length_from_the_header():
     # the reference's behaviour (frame_header = 0) swallows the following frames into the first packet
     frames0, _, _, _ = ORC.stream_demod(sf, x, mtu=1000, pkt_cap=16)
     assert len(frames0) < len(syms)
+
+
+@pytest.mark.parametrize("sf", [7, 8, 10, 12])
+def test_c_oracle_agrees_with_the_independent_python_statement(sf):
+    """tests/_std_python.py is the script that first decoded the capture, written before std_chain.c: frames encoded by
+    the C oracle must decode in it, for every coding rate, with and without LDRO and CRC."""
+    from _std_python import decode
+    rng = np.random.default_rng(100 + sf)
+    for cr in (1, 2, 3, 4):
+        for ldro in (False, True):
+            for crc in (False, True):
+                for n in (1, 2, 5, 31, 64):
+                    pay = rng.integers(0, 256, n, dtype=np.uint8)
+                    sym = ORC.std_encode(std_cfg(sf, cr, ldro, False, crc), pay)
+                    ln, has_crc, cr_rx, chk, data, _, ok = decode(sym, sf, ldro)
+                    assert (ln, has_crc, cr_rx) == (n, int(crc), cr) and data == bytes(pay), (sf, cr, ldro, crc, n)
+                    assert chk == ORC.std_header_checksum(n >> 4, n & 15, cr << 1 | int(crc))
+                    assert ok is (True if crc else None)
+    x = np.ascontiguousarray(capture()[0::2])
+    frames, _, _, _ = ORC.stream_demod(7, x, mtu=33, pkt_cap=32)
+    assert [decode(f, 7)[4] for f in frames] == [f"hello world: {k}".encode() for k in range(16)]
+    assert all(decode(f, 7)[6] for f in frames)
