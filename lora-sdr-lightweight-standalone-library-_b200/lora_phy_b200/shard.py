@@ -39,6 +39,28 @@ def gather_records(local, dist, out=None):
     return out
 
 
+def ragged_counts(n_local, dist, device=None):
+    """Record counts of every rank (a gateway's ranks own different numbers of packets: channels are balanced by
+    samples, not by packets).  One small all-gather at set-up time.  -> list of ints, rank order."""
+    import torch
+    mine = torch.tensor([int(n_local)], dtype=torch.int64, device=device)
+    parts = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(parts, mine)
+    return [int(p.item()) for p in parts]
+
+
+def gather_ragged_records(local_padded, dist, out=None):
+    """All-gather of per-packet records when ranks hold different counts: every rank passes a buffer of the SAME
+    padded length (max over `ragged_counts`), rows past its own count are ignored by the reader.  -> [world * n_max,
+    stride]; use `valid_rows` to walk it."""
+    return gather_records(local_padded, dist, out=out)
+
+
+def valid_rows(counts, n_max):
+    """(rank, first_row, n_rows) of every rank's valid records inside a gather_ragged_records result."""
+    return [(r, r * n_max, c) for r, c in enumerate(counts)]
+
+
 def stream_segments(count, n_segments, n, mtu=256, preamble_symbols=16):
     """Cut one long capture of `count` samples into `n_segments` pieces for the frame synchroniser (SURVEY.md 8e,
     "overlap-save by one maximum frame").  Segment k OWNS [own_lo, own_hi) -- a partition of [0, count) -- and READS

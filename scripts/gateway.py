@@ -39,7 +39,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     import torch
     import lora_phy_b200 as L
-    from lora_phy_b200.shard import assign_channels
+    from lora_phy_b200.shard import assign_channels, gather_ragged_records, ragged_counts, valid_rows
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
@@ -80,11 +80,7 @@ def main():
                           out=torch.zeros((n, L.PAYLOAD_STRIDE), dtype=torch.uint8, device="cuda"),
                           res=torch.zeros((n, 16), dtype=torch.uint8, device="cuda")))
     n_mine = sum(i["n"] for i in items)
-    counts = torch.tensor([n_mine], dtype=torch.int64, device="cuda")
-    all_counts = [counts.clone() for _ in range(world)]
-    if dist is not None:
-        dist.all_gather(all_counts, counts)
-    all_counts = [int(c.item()) for c in all_counts]
+    all_counts = ragged_counts(n_mine, dist, device="cuda") if dist is not None else [n_mine]
     n_max = max(all_counts)
     rec = torch.zeros((n_max, REC), dtype=torch.uint8, device="cuda")
     gathered = torch.zeros((world * n_max, REC), dtype=torch.uint8, device="cuda") if dist is not None else rec
@@ -103,7 +99,7 @@ def main():
 
     def gather():
         if dist is not None:  # the only NVLink traffic of a step
-            dist.all_gather_into_tensor(gathered, rec)
+            gather_ragged_records(rec, dist, out=gathered)
 
     def step():
         compute()
@@ -165,8 +161,8 @@ def main():
         g = gathered.cpu().numpy()
         seen = set()
         ok_gathered = 0
-        for r in range(world):
-            rows = g[r * n_max:r * n_max + all_counts[r]]
+        for _, first, n_rows in valid_rows(all_counts, n_max):
+            rows = g[first:first + n_rows]
             ids = np.ascontiguousarray(rows[:, ID_AT:REC]).view(np.uint32).reshape(-1, 2)
             seen.update(zip(ids[:, 0].tolist(), ids[:, 1].tolist()))
             ok_gathered += int((np.ascontiguousarray(rows[:, 0:16]).view(L.CHAIN_RESULT).reshape(-1)["crc_ok"] == 1).sum())

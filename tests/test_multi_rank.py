@@ -61,3 +61,46 @@ def test_record_gather_world_size_2_gloo():
     for p in procs:
         p.join(timeout=60)
     assert [r[1] for r in res] == [True, True] and all(r[2] == 11.0 for r in res)
+
+
+def _ragged_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    from lora_phy_b200.shard import assign_channels, gather_ragged_records, ragged_counts, valid_rows
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # a small gateway: channels of very different packet counts, balanced by samples (scripts/gateway.py does the same)
+    rng = np.random.default_rng(2)
+    sfs = rng.integers(7, 13, 50)
+    packets = {7: 91, 8: 46, 9: 27, 10: 13, 11: 8, 12: 4}
+    samples = [packets[int(s)] * 40 * (1 << int(s)) for s in sfs]
+    mine = assign_channels(samples, world)[rank]
+    ids = [(c, k) for c in mine for k in range(packets[int(sfs[c])])]
+    counts = ragged_counts(len(ids), dist)
+    n_max = max(counts)
+    rec = torch.zeros((n_max, 8), dtype=torch.uint8)
+    rec[:len(ids)] = torch.from_numpy(np.asarray(ids, np.uint32).view(np.uint8).reshape(len(ids), 8))
+    out = gather_ragged_records(rec, dist).numpy()
+    seen = set()
+    for r, first, n in valid_rows(counts, n_max):
+        got = np.ascontiguousarray(out[first:first + n]).view(np.uint32).reshape(-1, 2)
+        seen.update(map(tuple, got.tolist()))
+    want = {(c, k) for c in range(50) for k in range(packets[int(sfs[c])])}
+    q.put((rank, seen == want and counts[rank] == len(ids) and len(set(counts)) > 1))
+    dist.destroy_process_group()
+
+
+def test_ragged_record_gather_world_size_2_gloo():
+    """Ranks of a gateway hold different packet counts: padded all-gather + per-rank counts must cover every
+    (channel, packet) exactly once."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_ragged_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert [r[1] for r in res] == [True, True]
