@@ -275,7 +275,8 @@ typedef struct lora_b200_stream_result {
     uint32_t n_symbols;    /* symbols stored (<= max_symbols) */
 } lora_b200_stream_result;
 
-/* Samples in one generated frame: (10 + 2 + 2 + n_symbols + padding) * N*osr + N*osr/4. */
+/* Samples in one generated frame: (10 + 2 + 2 + n_symbols + max(padding, 1)) * N*osr + N*osr/4 -- the block counts a
+ * padding symbol before it compares with the setting (LoRa-SDR/LoRaMod.cpp:219-221), so 0 behaves like 1. */
 size_t lora_b200_frame_samples(const lora_b200_ctx* ctx, size_t n_symbols, unsigned padding);
 int lora_b200_frame_modulate_batch(lora_b200_ctx* ctx, const uint16_t* d_symbols, size_t n_packets, size_t n_symbols,
                                    size_t symbol_stride, float amplitude, uint8_t sync, unsigned padding,

@@ -432,7 +432,7 @@ __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModA
         phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
     }
     // :224-226 zero padding
-    const size_t pad = (size_t)a.padding * NN;
+    const size_t pad = (size_t)(a.padding ? a.padding : 1u) * NN; // the counter is incremented before the test (:219-221)
     for (int q = 0; q < warp_live; ++q)
         for (size_t i = lane; i < pad; i += 32) a.iq[(size_t)(pk0 + q) * a.packet_stride + at + i] = make_float2(0.0f, 0.0f);
 }
@@ -488,7 +488,7 @@ void build_stream_tables(int sf, std::vector<float2>& up, std::vector<float2>& d
 size_t frame_samples(int sf, int osr, size_t n_symbols, unsigned padding)
 {
     const size_t nn = ((size_t)1 << sf) * (size_t)osr;
-    return 14 * nn + nn / 4 + n_symbols * nn + (size_t)padding * nn;
+    return 14 * nn + nn / 4 + n_symbols * nn + (size_t)(padding ? padding : 1u) * nn; // LoRaMod.cpp:219-221: never fewer than one
 }
 
 cudaError_t launch_stream_detect(int sf, const StreamDetectArgs& a, int sm_count, cudaStream_t st)

@@ -32,7 +32,10 @@ size_t orc_frame_modulate(unsigned sf, unsigned ovs, const uint16_t* symbols, si
 {
     const int N = 1 << sf;
     const size_t NN = (size_t)N * ovs;
-    const size_t total = (10 + 2 + 2) * NN + NN / 4 + n_sym * NN + (size_t)padding * NN;
+    /* :217-228: STATE_PADSYMBOLS increments its counter BEFORE comparing it with _padding, so a padding of 0 still
+     * produces one zero symbol (pinned against the compiled block, tests/test_oracle_vs_pothos.py) */
+    const size_t n_pad = padding ? padding : 1;
+    const size_t total = (10 + 2 + 2) * NN + NN / 4 + n_sym * NN + n_pad * NN;
     if (!out) return total;
     float phase = 0.0f; /* :131 _phaseAccum = 0 at every packet */
     size_t pos = 0;
@@ -54,7 +57,7 @@ size_t orc_frame_modulate(unsigned sf, unsigned ovs, const uint16_t* symbols, si
         const float f = (float)((2 * M_PI * sym) / (double)NN);
         pos += (size_t)orc_gen_chirp(out + pos, N, (int)ovs, (int)NN, f, 0, ampl, &phase, 1.0f);
     }
-    for (size_t i = 0; i < (size_t)padding * NN; ++i) { out[pos].re = 0.0f; out[pos].im = 0.0f; ++pos; } /* :224-226 */
+    for (size_t i = 0; i < n_pad * NN; ++i) { out[pos].re = 0.0f; out[pos].im = 0.0f; ++pos; } /* :224-226 */
     return pos;
 }
 

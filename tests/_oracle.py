@@ -8,6 +8,7 @@ helpers below work on either.  Nothing in the product imports this module.
 import ctypes as C
 import os
 import subprocess
+import threading
 
 import numpy as np
 
@@ -65,11 +66,26 @@ class Lib:
     def __init__(self, path, prefix):
         self.lib = C.CDLL(path)
         self.prefix = prefix
+        self._bound = {}
+        self._lock = threading.Lock()
 
     def fn(self, name, restype, argtypes):
-        f = getattr(self.lib, f"{self.prefix}_{name}")
-        f.restype, f.argtypes = restype, argtypes
+        """The exported function `<prefix>_<name>` with its prototype bound ONCE.  The returned object is a private
+        ctypes function pointer per (name, prototype): `restype`/`argtypes` are never assigned on a call path, so
+        worker threads calling the same door cannot rebuild each other's converters (the round-1 bench crash)."""
+        key = (name, restype, tuple(argtypes))
+        f = self._bound.get(key)
+        if f is None:
+            with self._lock:
+                f = self._bound.get(key)
+                if f is None:
+                    proto = C.CFUNCTYPE(restype, *argtypes)
+                    f = proto((f"{self.prefix}_{name}", self.lib))
+                    self._bound[key] = f
         return f
+
+    def has(self, name):
+        return hasattr(self.lib, f"{self.prefix}_{name}")
 
     # ---- DSP ------------------------------------------------------------------------------------
     def gen_chirp(self, N, osr, NN, f0, down, ampl, phase, bw_scale=1.0):
@@ -281,11 +297,18 @@ class Lib:
         sym = np.zeros(pkt_cap * mtu, np.int16)
         plen, pstart, perr = np.zeros(pkt_cap, np.uint32), np.zeros(pkt_cap, np.uint64), np.zeros(pkt_cap, np.int32)
         consumed = C.c_uint64()
-        n = self.fn("stream_demod_hdr", C.c_size_t, [C.c_uint, C.c_ubyte, C.c_float, C.c_size_t, C.c_int, c64p, C.c_size_t,
-                                                 C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
-                                                 C.c_size_t, C.POINTER(C.c_uint64)])(
-            sf, sync, thresh, mtu, frame_header, samples, len(samples), sym.ctypes.data, len(sym), plen.ctypes.data,
-            pstart.ctypes.data, perr.ctypes.data, pkt_cap, C.byref(consumed))
+        tail = [c64p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                C.POINTER(C.c_uint64)]
+        rest = (samples, len(samples), sym.ctypes.data, len(sym), plen.ctypes.data, pstart.ctypes.data, perr.ctypes.data,
+                pkt_cap, C.byref(consumed))
+        if self.has("stream_demod_hdr"):
+            n = self.fn("stream_demod_hdr", C.c_size_t, [C.c_uint, C.c_ubyte, C.c_float, C.c_size_t, C.c_int] + tail)(
+                sf, sync, thresh, mtu, frame_header, *rest)
+        else:   # the compiled Pothos block: the reference's behaviour only
+            assert frame_header == 0
+            n = self.fn("stream_demod", C.c_size_t, [C.c_uint, C.c_ubyte, C.c_float, C.c_size_t] + tail)(
+                sf, sync, thresh, mtu, *rest)
+        assert n != C.c_size_t(-1).value, "the block threw"
         n = min(n, pkt_cap)
         pk, o = [], 0
         for k in range(n):
@@ -313,3 +336,6 @@ if not os.path.exists(_orc_path):
     build_oracle()
 ORC = Lib(_orc_path, "orc")
 REF = _load(os.path.join(ORACLE_DIR, "_ref", "liblora_ref.so"), "ref")
+# the four upstream Pothos blocks, unmodified, behind oracle/pothos_stub (doors: chain_encode, chain_decode,
+# frame_modulate, stream_demod -- same signatures as the orc_ ones)
+POTHOS = _load(os.path.join(ORACLE_DIR, "_ref", "liblora_pothos_ref.so"), "pothos")
