@@ -177,75 +177,152 @@ class Workload:
 
 # ---- the reference's CPU path, timed on the host cores ---------------------------------------------------
 def cpu_reference_time(host_items, threads):
-    """host_items: [(sf, iq complex64 [P, count], nsym)].  Runs the reference pipeline
-    caller-dechirp -> lora_demodulate (tests/performance_test.cpp:109-116) on every packet with oracle/_ref
-    (the unmodified reference, kind "reference") or, where that was never built, the C restatement (kind
-    "port"), plus the restated chain decode; `threads` host threads, one workspace each (ctypes releases
-    the GIL).  -> (seconds, samples, kind)."""
+    """host_items: [(sf, iq complex64 [P, count], nsym)].  The reference pipeline of tests/performance_test.cpp:92-116
+    -- workspace and down-chirp built once per thread OUTSIDE the timed loop, then per packet caller-dechirp ->
+    lora_demodulate -- followed by the full chain decode, all in native code on `threads` host threads:
+    oracle/_ref/liblora_ref.so (the unmodified src/phy/*.cpp; `ref_legacy_batch`) and oracle/_ref/liblora_pothos_ref.so
+    (the unmodified LoRa-SDR/LoRaDecoder.cpp; `pothos_chain_decode_batch`), kind "reference".  Where those were never
+    built the C restatement runs instead (kind "port", python thread pool over the thread-safe ctypes doors).
+    -> (seconds, samples, kind, crc-ok packets)."""
     import ctypes as C
+    from _oracle import ORC, REF, POTHOS, ChainCfg, chain_cfg as orc_cfg, c64p, u16p, u8p
+
+    samples = sum(iq.size for _, iq, _ in host_items)
+    if REF is not None and REF.has("legacy_batch"):
+        demod = REF.fn("legacy_batch", C.c_double, [C.c_uint, C.c_uint, c64p, C.c_size_t, C.c_size_t, C.c_uint, u16p,
+                                                    C.c_size_t, C.c_void_p, C.c_void_p])
+        decode = None
+        if POTHOS is not None and POTHOS.has("chain_decode_batch"):
+            decode = POTHOS.fn("chain_decode_batch", C.c_double,
+                               [C.POINTER(ChainCfg), u16p, C.c_size_t, C.c_size_t, C.c_size_t, u8p, C.c_size_t,
+                                np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS"), C.c_uint])
+        dt, ok = 0.0, 0
+        for sf, iq, nsym in host_items:
+            iq = np.ascontiguousarray(iq)
+            packets, count = iq.shape
+            sym = np.zeros((packets, nsym), np.uint16)
+            t = demod(sf, 125000, iq, packets, count, threads, sym, nsym, None, None)
+            assert t >= 0.0
+            dt += t
+            cfg = orc_cfg(sf, RDD)
+            if decode is not None:
+                out = np.zeros((packets, 64), np.uint8)
+                nb = np.zeros(packets, np.int64)
+                t = decode(C.byref(cfg), sym, packets, nsym, nsym, out, 64, nb, threads)
+                assert t >= 0.0
+                dt += t
+                ok += int((nb == PAYLOAD_LEN).sum())     # crcc on: a packet whose CRC fails is dropped (LoRaDecoder.cpp:371)
+            else:
+                t0 = time.perf_counter()
+                ok += sum(ORC.chain_decode(cfg, sym[p])[2].crc_ok for p in range(packets))
+                dt += time.perf_counter() - t0
+        return dt, samples, "reference", ok
+
     from concurrent.futures import ThreadPoolExecutor
-    from _oracle import ORC, REF, Metrics, chain_cfg as orc_cfg, c64p, u16p
-
-    kind = "reference" if REF is not None else "port"
-    tasks = []
-    for sf, iq, nsym in host_items:
-        chunk = max(1, len(iq) // (threads * 4))
-        for a in range(0, len(iq), chunk):
-            tasks.append((sf, iq, nsym, a, min(len(iq), a + chunk)))
-
-    if REF is not None:
-        create = REF.fn("legacy_create", C.c_void_p, [C.c_uint, C.c_int, C.c_size_t, C.c_uint])
-        destroy = REF.fn("legacy_destroy", None, [C.c_void_p])
-        run = REF.fn("legacy_dechirp_demodulate", C.c_size_t, [C.c_void_p, c64p, C.c_size_t, u16p,
-                                                               C.POINTER(C.c_uint8), C.POINTER(Metrics)])
 
     def work(task):
-        sf, iq, nsym, a, b = task
-        count = iq.shape[1]
-        out = np.zeros(nsym + 2, np.uint16)
+        sf, iq, a, b = task
+        n = 1 << sf
+        down = ORC.gen_chirp(n, 1, n, 0.0, True, 1.0, 0.0, 1.0)[0]
         cfg = orc_cfg(sf, RDD)
         ok = 0
-        if REF is not None:
-            h = create(sf, 0, count, 125000)
-            sync, m = C.c_uint8(), Metrics()
-            for p in range(a, b):
-                k = run(h, iq[p], count, out, C.byref(sync), C.byref(m))
-                ok += ORC.chain_decode(cfg, out[:k])[2].crc_ok
-            destroy(h)
-        else:
-            n = 1 << sf
-            down = ORC.gen_chirp(n, 1, n, 0.0, True, 1.0, 0.0, 1.0)[0]
-            for p in range(a, b):
-                x = iq[p].reshape(-1, n)
-                re = (x.real * down.real[None]).astype(np.float32) - (x.imag * down.imag[None]).astype(np.float32)
-                im = (x.real * down.imag[None]).astype(np.float32) + (x.imag * down.real[None]).astype(np.float32)
-                _, sym, _, _ = ORC.lora_demodulate(sf, (re + 1j * im).astype(np.complex64).reshape(-1))
-                ok += ORC.chain_decode(cfg, sym)[2].crc_ok
+        for p in range(a, b):
+            x = iq[p].reshape(-1, n)
+            re = (x.real * down.real[None]).astype(np.float32) - (x.imag * down.imag[None]).astype(np.float32)
+            im = (x.real * down.imag[None]).astype(np.float32) + (x.imag * down.real[None]).astype(np.float32)
+            _, sym, _, _ = ORC.lora_demodulate(sf, (re + 1j * im).astype(np.complex64).reshape(-1))
+            ok += ORC.chain_decode(cfg, sym)[2].crc_ok
         return ok
 
+    tasks = []
+    for sf, iq, _ in host_items:
+        chunk = max(1, len(iq) // (threads * 4))
+        tasks += [(sf, iq, a, min(len(iq), a + chunk)) for a in range(0, len(iq), chunk)]
     t0 = time.perf_counter()
     with ThreadPoolExecutor(threads) as ex:
         ok = sum(ex.map(work, tasks))
-    dt = time.perf_counter() - t0
-    samples = sum(iq.size for _, iq, _ in host_items)
-    return dt, samples, kind, ok
+    return time.perf_counter() - t0, samples, "port", ok
 
 
-def cpu_synth(packets, seed=0):
-    """CPU-side synthesis for the reference arm (none of this repo's kernels on that path): oracle chain
-    encoder, the reference's own lora_modulate where oracle/_ref exists, numpy AWGN."""
-    from _oracle import ORC, REF, chain_cfg as orc_cfg
-    mod = REF if REF is not None else ORC
+def performance_test_runs():
+    """The reference's own benchmark, tests/performance_test.cpp UNMODIFIED (1000 packets x 32 bytes, modulate + caller
+    dechirp + lora_demodulate, one thread), with tests/profiles.yaml extended to SF7-SF12 in a scratch directory:
+    once linked against the reference itself (oracle/_ref/performance_test) and once against this repo's drop-in
+    (bin/ref_performance_test, every call a single-packet GPU call).  Also `rx_runner` wall time on the golden capture
+    for both.  -> dict, or None where the binaries were never built."""
+    import tempfile
+    out = {}
+    cand = {"reference": os.path.join(ROOT, "oracle", "_ref", "performance_test"),
+            "b200_dropin": os.path.join(ROOT, "lora-sdr-lightweight-standalone-library-_b200", "bin", "ref_performance_test")}
+    with tempfile.TemporaryDirectory() as tmp:
+        os.makedirs(os.path.join(tmp, "tests"))
+        with open(os.path.join(tmp, "tests", "profiles.yaml"), "w") as f:
+            for sf in SFS:
+                f.write(f"-\n  name: sf{sf}_bw125_cr45\n  sf: {sf}\n  bw: 125000\n  cr: 4/5\n")
+        for who, exe in cand.items():
+            if not os.path.exists(exe):
+                continue
+            try:
+                subprocess.run([exe], cwd=tmp, env=dict(os.environ, RUN_ID=who), check=True, timeout=240,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                rows = open(os.path.join(tmp, "logs", f"performance_{who}.csv")).read().strip().splitlines()[1:]
+                out[who] = {r.split(",")[1]: {"pps": float(r.split(",")[4]), "cycles_per_symbol": float(r.split(",")[5])}
+                            for r in rows}
+            except Exception as e:  # a failed side program must never cost the bench line
+                out[who] = {"error": repr(e)[:200]}
+    cap = os.path.join(ROOT, "tests", "golden", "capture_sf7.npz")
+    runners = {"reference": os.path.join(ROOT, "oracle", "_ref", "rx_runner"),
+               "b200_dropin": os.path.join(ROOT, "lora-sdr-lightweight-standalone-library-_b200", "bin", "rx_runner")}
+    if os.path.exists(cap):
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, "capture.iq")
+            np.load(cap)["iq"].astype(np.complex64).tofile(path)
+            wall = {}
+            for who, exe in runners.items():
+                if not os.path.exists(exe):
+                    continue
+                try:
+                    best = None
+                    for _ in range(3):
+                        t0 = time.perf_counter()
+                        subprocess.run([exe, f"--in={path}", "--sf=7", "--cr=1", "--bw=125000", "--report-offsets"],
+                                       check=True, timeout=120, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                        dt = time.perf_counter() - t0
+                        best = dt if best is None else min(best, dt)
+                    wall[who] = round(best, 4)
+                except Exception as e:
+                    wall[who] = repr(e)[:200]
+            out["rx_runner_wall_s_golden_capture"] = wall
+    return out or None
+
+
+def cpu_synth(packets, threads, seed=0):
+    """CPU-side synthesis for the reference arm (none of this repo's kernels on that path): the chain encoder
+    restatement (pinned to LoRaEncoder.cpp by tests/test_oracle_vs_pothos.py), the reference's own lora_modulate where
+    oracle/_ref exists, numpy AWGN."""
+    import ctypes as C
+    from _oracle import ORC, REF, chain_cfg as orc_cfg, c64p, u16p
     rng = np.random.default_rng(seed)
     items = []
     for sf in SFS:
         nsym = symbols_per_packet(sf)
-        iq = np.zeros((packets, (nsym + 2) << sf), np.complex64)
+        count = (nsym + 2) << sf
+        sym = np.zeros((packets, nsym), np.uint16)
+        cfg = orc_cfg(sf, RDD)
         for p in range(packets):
-            sym = ORC.chain_encode(orc_cfg(sf, RDD), bytes(rng.integers(0, 256, PAYLOAD_LEN, dtype=np.uint8)))
-            clean = mod.lora_modulate(sym, sf)
-            sigma = 10.0 ** (-rng.choice(SNRS) / 20.0) / np.sqrt(2.0)
-            iq[p] = clean + (rng.standard_normal(len(clean)) + 1j * rng.standard_normal(len(clean))) * sigma
+            sym[p] = ORC.chain_encode(cfg, bytes(rng.integers(0, 256, PAYLOAD_LEN, dtype=np.uint8)))
+        iq = np.zeros((packets, count), np.complex64)
+        if REF is not None and REF.has("modulate_batch"):
+            REF.fn("modulate_batch", None, [u16p, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_float, C.c_uint8, c64p,
+                                            C.c_uint])(sym, packets, nsym, sf, 125000, 1.0, 0x12, iq, threads)
+        else:
+            for p in range(packets):
+                iq[p] = ORC.lora_modulate(sym[p], sf)
+        sigma = (10.0 ** (-rng.choice(SNRS, packets) / 20.0) / np.sqrt(2.0)).astype(np.float32)
+        for a in range(0, packets, 256):        # in slabs: the SF12 batch is 1.7 GB
+            sl = slice(a, min(packets, a + 256))
+            noise = rng.standard_normal((sl.stop - sl.start, count, 2), dtype=np.float32)
+            iq[sl] += (noise[..., 0] + 1j * noise[..., 1]) * sigma[sl, None]
         items.append((sf, iq, nsym))
     return items
 
@@ -255,21 +332,22 @@ def run_reference(args, rank):
         return
     threads = os.cpu_count() or 1
     packets = args.ref_packets
-    items = cpu_synth(packets)
+    items = cpu_synth(packets, threads)
     for _ in range(args.warmup):
         cpu_reference_time(items, threads)
-    t, samples, kind = 0.0, 0, "port"
+    t, samples, kind, ok = 0.0, 0, "port", 0
     for _ in range(args.steps):
-        dt, s, kind, _ = cpu_reference_time(items, threads)
+        dt, s, kind, ok = cpu_reference_time(items, threads)
         t += dt; samples += s
     v = samples / t / 1e6
-    sample = f"{packets} packets per SF (SF7-12), {samples // args.steps} samples per step"
+    sample = f"{packets} packets per SF (SF7-12), {samples // args.steps} samples per step, {ok} CRC-ok packets"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[1]: SF7-SF12 sweep, AWGN -20..+10 dB, demod + full decode",
-                   "payload_bytes": PAYLOAD_LEN, "cr": "4/5", "header": "explicit", "crc": True, "sample": sample},
+        "config": {"workload": "configs[1]: SF7-SF12 sweep, synthetic AWGN -20..+10 dB, demod + full decode",
+                   "payload_bytes": PAYLOAD_LEN, "cr": "4/5", "header": "explicit", "crc": True, "bw_hz": 125000, "osr": 1,
+                   "demod_semantics": "legacy_dechirp", "sample": sample},
         "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
@@ -283,10 +361,11 @@ def main():
     ap.add_argument("--packets", type=int, default=65536, help="packets per SF per GPU")
     ap.add_argument("--e2e-packets", type=int, default=2048)
     ap.add_argument("--cpu-packets", type=int, default=2048)
-    ap.add_argument("--ref-packets", type=int, default=128)
+    ap.add_argument("--ref-packets", type=int, default=2048)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace"])
     ap.add_argument("--no-int16", action="store_true", help="skip the extra int16-ingest end-to-end leg")
+    ap.add_argument("--no-perf-test", action="store_true", help="skip the reference's own performance_test / rx_runner runs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -471,20 +550,29 @@ def main():
                                     "Msamples_s": round(i["samples"] * max(k_sf, 1) / (ms_sf * 1e-3) / 1e6, 1) if ms_sf > 0 else 0.0,
                                     "crc_ok": crc_ok[i["sf"]], "symbols_eq_tx": sym_ok[i["sf"]]}
 
-    # cpu_baseline: the same packets as the e2e sample, the reference's CPU path on this box's host cores
-    cpu = None
+    # cpu_baseline: the same packets as the e2e sample, the reference's CPU path on this box's host cores.  Whatever
+    # happens in this leg, the GPU measurement above is printed: a failure becomes "cpu_baseline": null + "cpu_error".
+    cpu, cpu_error = None, None
     if world == 1:
-        # same packets, the reference's CPU path on this box's host cores
-        pc = min(args.cpu_packets, pe)
-        threads = os.cpu_count() or 1
-        host_items = [(i["sf"], h_iq[:pc], i["tx"].shape[1]) for i, h_iq, _, _, _, _ in pinned]
-        dt_c, s_c, kind, ok_cpu = cpu_reference_time(host_items, threads)
-        # live parity check: CRC-ok packets the CPU reference path finds in this sample vs what the GPU found
-        ok_gpu = int(sum((i["results"][:pc].cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)["crc_ok"] == 1).sum()
-                         for i in wl.items))
-        cpu = {"value": s_c / dt_c / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
-               "sample": f"first {pc} packets per SF of the same workload ({s_c} samples, {dt_c:.1f} s wall)",
-               "crc_ok_packets_cpu": int(ok_cpu), "crc_ok_packets_gpu_same_sample": ok_gpu}
+        try:
+            pc = min(args.cpu_packets, pe)
+            threads = os.cpu_count() or 1
+            host_items = [(i["sf"], h_iq[:pc], i["tx"].shape[1]) for i, h_iq, _, _, _, _ in pinned]
+            cpu_reference_time([(sf, iq[:64], n) for sf, iq, n in host_items], threads)          # warm the pages and threads
+            dt_c, s_c, kind, ok_cpu = cpu_reference_time(host_items, threads)
+            # live parity check: CRC-ok packets the CPU reference path (compiled LoRaDecoder::work) finds in this sample
+            # vs what the GPU found on the same packets
+            ok_gpu = int(sum((i["results"][:pc].cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)["crc_ok"] == 1).sum()
+                             for i in wl.items))
+            cpu = {"value": s_c / dt_c / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
+                   "sample": f"first {pc} packets per SF of the same workload ({s_c} samples, {dt_c:.1f} s in the timed loops)",
+                   "pipeline": "tests/performance_test.cpp:92-116 per packet (workspace + down-chirp once per thread, outside "
+                               "the timed loop) + LoRaDecoder::work, native threads",
+                   "crc_ok_packets_cpu": int(ok_cpu), "crc_ok_packets_gpu_same_sample": ok_gpu}
+            if not args.no_perf_test:
+                cpu["performance_test"] = performance_test_runs()
+        except Exception as e:
+            cpu_error = repr(e)[:300]
 
     line = {
         "metric": METRIC, "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
@@ -515,8 +603,9 @@ def main():
         line["e2e"] = e2e
     if e2e_i16:
         line["e2e_int16"] = e2e_i16
-    if cpu:
-        line["cpu_baseline"] = cpu
+    line["cpu_baseline"] = cpu
+    if cpu_error:
+        line["cpu_error"] = cpu_error
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

@@ -220,6 +220,24 @@ int lora_b200_encode_host(lora_b200_ctx* ctx, const uint8_t* h_bytes, size_t n_b
 int lora_b200_decode_host(lora_b200_ctx* ctx, const uint16_t* h_symbols, size_t n_symbols, uint8_t* h_bytes,
                           size_t byte_cap, size_t* produced, int* crc_ok);
 int lora_b200_compensate_host(lora_b200_ctx* ctx, float cfo, float time_offset, lora_b200_c32* h_iq, size_t count);
+/* ---- stand-alone FFT and detector ------------------------------------------------------------------------------------
+ * kissfft<float>::transform (include/lora_phy/kissfft.hh:100-185) and LoRaDetector<float>::detect
+ * (include/lora_phy/LoRaDetector.hpp:39-74) for n_windows windows of N = 2^sf samples each, bit for bit the CPU's:
+ * the spectrum in natural bin order (inverse != 0: the plan built with inverse = true, kissfft.hh:24-29,176-181), and
+ * per window the first-strict-maximum bin of |X|^2, power and powerAvg in dB (minus 20*log10(N)) and the parabolic
+ * fIndex.  These are what include/lora_phy/kissfft.hh and LoRaDetector.hpp of this build forward to. */
+typedef struct {
+    uint32_t index;      /* LoRaDetector::detect return value */
+    float power;         /* :64 */
+    float power_avg;     /* :63 */
+    float f_index;       /* :66-71 */
+} lora_b200_detect_result;
+int lora_b200_fft_detect_batch(lora_b200_ctx* ctx, const lora_b200_c32* d_in, size_t n_windows, int inverse,
+                               lora_b200_c32* d_spectrum /* nullable */, lora_b200_detect_result* d_results /* nullable */,
+                               void* stream);
+int lora_b200_fft_detect_host(lora_b200_ctx* ctx, const lora_b200_c32* h_in, size_t n_windows, int inverse,
+                              lora_b200_c32* h_spectrum /* nullable */, lora_b200_detect_result* h_results /* nullable */);
+
 /* Batched host-buffer demod + chain decode: the end-to-end call bench.py times (pinned or pageable host
  * memory in, payloads and results out). */
 int lora_b200_receive_host(lora_b200_ctx* ctx, int mode, const lora_b200_chain_cfg* cfg,

@@ -20,6 +20,7 @@
 #include "code_kernels.h"
 #include "demod_fast.h"
 #include "demod_kernels.h"
+#include "fft_kernels.h"
 #include "host_tables.h"
 #include "mod_kernels.h"
 #include "std_kernels.h"
@@ -957,6 +958,60 @@ extern "C" int lora_b200_compensate_host(lora_b200_ctx* c, float cfo, float time
     a.offset = (off != 0 && static_cast<unsigned long long>(off < 0 ? -off : off) < count) ? off : 0; // :164,169
     CU(launch_compensate(a, st));
     CU(cudaMemcpyAsync(h_iq, a.out, sizeof(float2) * count, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return LORA_B200_OK;
+}
+
+// ---- stand-alone FFT and detector (kissfft.hh:100-185, LoRaDetector.hpp:39-74) -----------------------------------
+static_assert(sizeof(lora_b200_detect_result) == sizeof(DetectOut), "detector record must match the kernel's");
+
+extern "C" int lora_b200_fft_detect_batch(lora_b200_ctx* c, const lora_b200_c32* d_in, size_t n_windows, int inverse,
+                                          lora_b200_c32* d_spectrum, lora_b200_detect_result* d_results, void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (!d_in || (!d_spectrum && !d_results)) return fail(LORA_B200_EINVAL, "null buffer");
+    if (inverse && d_results) return fail(LORA_B200_EINVAL, "the detector runs on the forward transform");
+    if (n_windows == 0) return LORA_B200_OK;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    FftArgs a{};
+    a.in = reinterpret_cast<const float2*>(d_in);
+    a.n_windows = n_windows;
+    a.inverse = inverse != 0;
+    a.tw = c->d_tw;
+    a.power_scale = c->power_scale;
+    a.out = reinterpret_cast<float2*>(d_spectrum);
+    a.det = reinterpret_cast<DetectOut*>(d_results);
+    CU(launch_fft_detect(static_cast<int>(c->cfg.sf), a, c->sm_count, static_cast<cudaStream_t>(stream)));
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_fft_detect_host(lora_b200_ctx* c, const lora_b200_c32* h_in, size_t n_windows, int inverse,
+                                         lora_b200_c32* h_spectrum, lora_b200_detect_result* h_results)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    if (!h_in || (!h_spectrum && !h_results)) return fail(LORA_B200_EINVAL, "null buffer");
+    if (n_windows == 0) return LORA_B200_OK;
+    const size_t bytes = sizeof(float2) * n_windows * static_cast<size_t>(c->n);
+    cudaStream_t st;
+    float2 *d_in, *d_out;
+    DetectOut* d_det;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        CU(cudaSetDevice(c->device));
+        CU(c->s_iq.reserve(bytes));
+        CU(c->s_payload.reserve(bytes));
+        CU(c->s_results.reserve(sizeof(DetectOut) * n_windows));
+        st = c->stream;
+        d_in = c->s_iq.as<float2>(); d_out = c->s_payload.as<float2>(); d_det = c->s_results.as<DetectOut>();
+        CU(cudaMemcpyAsync(d_in, h_in, bytes, cudaMemcpyHostToDevice, st));
+    }
+    const int rc = lora_b200_fft_detect_batch(c, reinterpret_cast<const lora_b200_c32*>(d_in), n_windows, inverse,
+                                              h_spectrum ? reinterpret_cast<lora_b200_c32*>(d_out) : nullptr,
+                                              h_results ? reinterpret_cast<lora_b200_detect_result*>(d_det) : nullptr, st);
+    if (rc != LORA_B200_OK) return rc;
+    if (h_spectrum) CU(cudaMemcpyAsync(h_spectrum, d_out, bytes, cudaMemcpyDeviceToHost, st));
+    if (h_results) CU(cudaMemcpyAsync(h_results, d_det, sizeof(DetectOut) * n_windows, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     return LORA_B200_OK;
 }

@@ -226,7 +226,10 @@ size_t lora_demodulate(lora_demod_workspace* ws, const std::complex<float>* samp
     ws->fft_plan.device = c;
     const size_t step = ws->N * (osr ? osr : 1u);
     const size_t total = step ? sample_count / step : 0;
-    std::vector<uint16_t> tmp(total + 1);
+    // grow-only, per calling thread: no allocation once a packet length has been seen (tests/no_alloc_test.cpp's rule
+    // for the steady state)
+    static thread_local std::vector<uint16_t> tmp;
+    if (tmp.size() < total + 1) tmp.resize(total + 1);
     size_t n = 0;
     lora_b200_pkt_metrics m{};
     if (lora_b200_demodulate_host(c, LORA_B200_DEMOD_LEGACY, reinterpret_cast<const lora_b200_c32*>(samples), sample_count,
@@ -258,5 +261,41 @@ size_t lora_decode(const uint16_t* symbols, size_t symbol_count, uint8_t* out_by
         return 0;
     return produced;
 }
+
+// ---- kissfft<float>::transform / LoRaDetector<float>::detect (include/lora_phy/kissfft.hh, LoRaDetector.hpp) ----------
+namespace detail {
+
+static lora_b200_ctx* ctx_for_length(std::size_t nfft)
+{
+    const unsigned sf = deduce_sf(nfft);
+    if (sf < 2 || sf > 12 || (std::size_t(1) << sf) != nfft) return nullptr;
+    return registry().get(sf, 125000u, 1u, false);
+}
+
+int device_fft(std::size_t nfft, bool inverse, const std::complex<float>* src, std::complex<float>* dst)
+{ // kissfft.hh:100-103
+    lora_b200_ctx* c = ctx_for_length(nfft);
+    if (!c || !src || !dst) return -1;
+    return lora_b200_fft_detect_host(c, reinterpret_cast<const lora_b200_c32*>(src), 1, inverse ? 1 : 0,
+                                     reinterpret_cast<lora_b200_c32*>(dst), nullptr) == LORA_B200_OK ? 0 : -1;
+}
+
+int device_detect(std::size_t nfft, const std::complex<float>* src, std::complex<float>* spectrum, std::size_t* index,
+                  float* power, float* power_avg, float* f_index)
+{ // LoRaDetector.hpp:39-74
+    lora_b200_ctx* c = ctx_for_length(nfft);
+    if (!c || !src) return -1;
+    lora_b200_detect_result r{};
+    if (lora_b200_fft_detect_host(c, reinterpret_cast<const lora_b200_c32*>(src), 1, 0,
+                                  reinterpret_cast<lora_b200_c32*>(spectrum), &r) != LORA_B200_OK)
+        return -1;
+    if (index) *index = r.index;
+    if (power) *power = r.power;
+    if (power_avg) *power_avg = r.power_avg;
+    if (f_index) *f_index = r.f_index;
+    return 0;
+}
+
+} // namespace detail
 
 } // namespace lora_phy

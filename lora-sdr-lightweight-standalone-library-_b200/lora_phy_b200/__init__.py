@@ -61,6 +61,9 @@ STREAM_PACKET = np.dtype([("start", "<u8"), ("first_symbol", "<u4"), ("n_symbols
 STREAM_RESULT = np.dtype([("consumed", "<u8"), ("n_packets", "<u4"), ("n_symbols", "<u4")])
 
 
+DETECT_RESULT = np.dtype([("index", "<u4"), ("power", "<f4"), ("power_avg", "<f4"), ("f_index", "<f4")])
+
+
 class LoraB200Error(RuntimeError):
     pass
 
@@ -130,6 +133,8 @@ _SIGNATURES = {
                                              C.c_size_t, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lora_b200_receive_host_i8": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ChainCfg), C.c_void_p, C.c_size_t,
                                             C.c_size_t, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_fft_detect_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_fft_detect_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]),
     "lora_b200_frame_samples": (C.c_size_t, [C.c_void_p, C.c_size_t, C.c_uint]),
     "lora_b200_frame_modulate_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float,
                                                  C.c_uint8, C.c_uint, C.c_void_p, C.c_size_t, C.c_void_p]),
@@ -435,6 +440,24 @@ class Context:
         _check(self.lib.lora_b200_estimate_host(self.h, samples.ctypes.data_as(C.c_void_p), len(samples),
                                                 C.byref(cfo), C.byref(to)))
         return np.float32(cfo.value), np.float32(to.value)
+
+    def fft(self, windows, inverse=False):
+        """kissfft<float>::transform (kissfft.hh:100-185) of every row of `windows` (host array, N columns)."""
+        x = np.ascontiguousarray(windows, np.complex64).reshape(-1, self.n)
+        out = np.zeros_like(x)
+        _check(self.lib.lora_b200_fft_detect_host(self.h, x.ctypes.data_as(C.c_void_p), len(x), int(inverse),
+                                                  out.ctypes.data_as(C.c_void_p), None))
+        return out
+
+    def detect(self, windows, want_spectrum=False):
+        """LoRaDetector<float>::detect (LoRaDetector.hpp:39-74) per row -> DETECT_RESULT records [, spectrum]."""
+        x = np.ascontiguousarray(windows, np.complex64).reshape(-1, self.n)
+        res = np.zeros(len(x), DETECT_RESULT)
+        spec = np.zeros_like(x) if want_spectrum else None
+        _check(self.lib.lora_b200_fft_detect_host(self.h, x.ctypes.data_as(C.c_void_p), len(x), 0,
+                                                  spec.ctypes.data_as(C.c_void_p) if want_spectrum else None,
+                                                  res.ctypes.data_as(C.c_void_p)))
+        return (res, spec) if want_spectrum else res
 
     def compensate_offsets(self, cfo, time_offset, samples):
         """lora_phy::compensate_offsets (phy.cpp:147-176) on a copy of `samples`."""

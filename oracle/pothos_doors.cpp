@@ -135,6 +135,64 @@ extern "C" long pothos_chain_decode(const orc_chain_cfg* c, const uint16_t* symb
 }
 #endif
 
+#ifdef DOOR_DECODER
+#include <chrono>
+#include <thread>
+// LoRaDecoder::work over a batch, for bench.py's CPU leg: `threads` host threads, ONE block per thread configured
+// once, a packet message pushed and work() called per packet.  n_bytes[p] = bytes posted, -1 dropped, -2 no output;
+// out (payload_stride bytes per packet) receives the posted bytes.  Returns the seconds of the timed loops.
+extern "C" double pothos_chain_decode_batch(const orc_chain_cfg* c, const uint16_t* symbols, size_t packets, size_t nsym,
+                                            size_t symbol_stride, uint8_t* out, size_t payload_stride, long* n_bytes,
+                                            unsigned threads)
+{
+    if (!c || !symbols || !n_bytes || threads == 0) return -1.0;
+    if (threads > packets) threads = packets ? unsigned(packets) : 1u;
+    auto body = [&](unsigned t) {
+        try {
+            Zeroed<LoRaDecoder> dec;
+            dec->setSpreadFactor(c->sf);
+            dec->setSymbolSize(c->ppm);
+            dec->setCodingRate(cr_name(c->rdd));
+            dec->enableWhitening(c->whitening != 0);
+            dec->enableCrcc(c->crc != 0);
+            dec->enableInterleaving(c->interleaving != 0);
+            dec->enableExplicit(c->explicit_header != 0);
+            dec->enableHdr(c->hdr_out != 0);
+            dec->setDataLength(c->data_length);
+            dec->enableErrorCheck(c->error_check != 0);
+            dec->activate();
+            unsigned long long dropped = 0;
+            for (size_t p = packets * t / threads; p < packets * (t + 1) / threads; ++p) {
+                Pothos::Packet pkt;
+                pkt.payload = Pothos::BufferChunk(typeid(uint16_t), nsym);
+                std::memcpy(pkt.payload.as<void*>(), symbols + p * symbol_stride, nsym * sizeof(uint16_t));
+                dec->input(0)->pushMessage(Pothos::Object(pkt));
+                dec->work();
+                dec->signals.clear();
+                auto& posted = dec->output(0)->messages;
+                if (dec->getDropped() != dropped) { dropped = dec->getDropped(); n_bytes[p] = -1; }
+                else if (posted.empty()) n_bytes[p] = -2;
+                else {
+                    const Pothos::Packet& r = posted.front().extract<Pothos::Packet>();
+                    n_bytes[p] = long(r.payload.length);
+                    if (out) std::memcpy(out + p * payload_stride, r.payload.as<const void*>(),
+                                         r.payload.length < payload_stride ? r.payload.length : payload_stride);
+                }
+                posted.clear();
+            }
+        } catch (const std::exception&) {
+            for (size_t p = packets * t / threads; p < packets * (t + 1) / threads; ++p) n_bytes[p] = -100;
+        }
+    };
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < threads; ++t) pool.emplace_back(body, t);
+    body(0);
+    for (auto& th : pool) th.join();
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+#endif
+
 #ifdef DOOR_MOD
 #include "LoRaMod.cpp"
 

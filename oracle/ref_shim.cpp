@@ -11,8 +11,10 @@
 #include <lora_phy/LoRaDetector.hpp>
 #include <lora_phy/kissfft.hh>
 
+#include <chrono>
 #include <complex>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 typedef std::complex<float> cf;
@@ -55,6 +57,7 @@ uint8_t ref_chk_p64(uint8_t b, int* error) { bool e = *error != 0; const uint8_t
 uint8_t ref_enc_p64(uint8_t b) { return encodeParity64(b); }
 void ref_interleave(const uint8_t* cw, size_t ncw, uint16_t* sym, size_t ppm, size_t rdd) { diagonalInterleaveSx(cw, ncw, sym, ppm, rdd); }
 void ref_deinterleave(const uint16_t* sym, size_t nsym, uint8_t* cw, size_t ppm, size_t rdd) { diagonalDeterleaveSx(sym, nsym, cw, ppm, rdd); }
+void ref_deinterleave2(const uint16_t* sym, size_t nsym, uint8_t* cw, size_t ppm, size_t rdd) { diagonalDeterleaveSx2(sym, nsym, cw, ppm, rdd); }
 
 // ---- ChirpGenerator.hpp / kissfft.hh / LoRaDetector.hpp ---------------------------------------------------
 int ref_gen_chirp(cf* out, int N, int osr, int NN, float f0, int down, float ampl, float* phase, float bw_scale)
@@ -217,6 +220,79 @@ size_t ref_legacy_dechirp_demodulate(void* h, const cf* samples, size_t count, u
     for (size_t s = 0; s < count / N; ++s)
         for (size_t i = 0; i < N; ++i) l->dechirped[s * N + i] = samples[s * N + i] * l->down[i];
     return ref_legacy_demodulate(h, l->dechirped.data(), count, out, 1, out_sync, m);
+}
+
+
+// The timed CPU baseline of bench.py: the pipeline of tests/performance_test.cpp:92-116 (down-chirp and workspace built
+// once, OUTSIDE the timed loop; per packet: caller dechirp + lora_demodulate) over `packets` packets of `count` samples
+// each, shared out in contiguous ranges over `threads` host threads, one workspace per thread.  Writes the data symbols
+// (symbol_stride uint16 per packet) and the sync byte per packet; returns the seconds the timed loops took (threads
+// started after every workspace exists, steady_clock around start..join), or -1 on a bad argument.
+double ref_legacy_batch(unsigned sf, unsigned bw_hz, const cf* iq, size_t packets, size_t count, unsigned threads,
+                        uint16_t* out_symbols, size_t symbol_stride, uint8_t* out_sync, size_t* out_counts)
+{
+    if (!iq || !out_symbols || threads == 0 || sf < 2 || sf > 12) return -1.0;
+    if (threads > packets) threads = packets ? unsigned(packets) : 1u;
+    std::vector<void*> ws(threads);
+    for (unsigned t = 0; t < threads; ++t) ws[t] = ref_legacy_create(sf, 0, count, bw_hz);
+    const size_t total = count >> sf;
+    auto body = [&](unsigned t) {
+        const size_t a = packets * t / threads, b = packets * (t + 1) / threads;
+        std::vector<uint16_t> sym(total + 2);
+        for (size_t p = a; p < b; ++p) {
+            uint8_t sync = 0;
+            const size_t k = ref_legacy_dechirp_demodulate(ws[t], iq + p * count, count, sym.data(), &sync, nullptr);
+            std::memcpy(out_symbols + p * symbol_stride, sym.data(), sizeof(uint16_t) * (k < symbol_stride ? k : symbol_stride));
+            if (out_sync) out_sync[p] = sync;
+            if (out_counts) out_counts[p] = k;
+        }
+    };
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < threads; ++t) pool.emplace_back(body, t);
+    body(0);
+    for (auto& th : pool) th.join();
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (unsigned t = 0; t < threads; ++t) ref_legacy_destroy(ws[t]);
+    return dt;
+}
+
+// The same for the workspace API (phy.cpp demodulate(), which dechirps internally).
+double ref_ws_batch(const ref_params* prm, const cf* iq, size_t packets, size_t count, unsigned threads,
+                    uint16_t* out_symbols, size_t symbol_stride)
+{
+    if (!iq || !out_symbols || threads == 0) return -1.0;
+    if (threads > packets) threads = packets ? unsigned(packets) : 1u;
+    std::vector<void*> ws(threads);
+    for (unsigned t = 0; t < threads; ++t) ws[t] = ref_ws_create(prm);
+    auto body = [&](unsigned t) {
+        const size_t a = packets * t / threads, b = packets * (t + 1) / threads;
+        for (size_t p = a; p < b; ++p) ref_ws_demodulate(ws[t], iq + p * count, count, out_symbols + p * symbol_stride, symbol_stride, nullptr);
+    };
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < threads; ++t) pool.emplace_back(body, t);
+    body(0);
+    for (auto& th : pool) th.join();
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (unsigned t = 0; t < threads; ++t) ref_ws_destroy(ws[t]);
+    return dt;
+}
+
+// lora_modulate over a batch (CPU-side synthesis for bench.py --impl reference; not timed).
+void ref_modulate_batch(const uint16_t* symbols, size_t packets, size_t nsym, unsigned sf, unsigned bw_hz, float amplitude,
+                        uint8_t sync, cf* out, unsigned threads)
+{
+    const size_t count = (nsym + 2) << sf;
+    if (threads == 0) threads = 1;
+    auto body = [&](unsigned t) {
+        for (size_t p = packets * t / threads; p < packets * (t + 1) / threads; ++p)
+            lora_phy::lora_modulate(symbols + p * nsym, nsym, out + p * count, sf, 1, bw_of(bw_hz), amplitude, sync);
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < threads; ++t) pool.emplace_back(body, t);
+    body(0);
+    for (auto& th : pool) th.join();
 }
 
 } // extern "C"
