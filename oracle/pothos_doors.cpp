@@ -148,28 +148,27 @@ extern "C" double pothos_chain_decode_batch(const orc_chain_cfg* c, const uint16
     if (!c || !symbols || !n_bytes || threads == 0) return -1.0;
     if (threads > packets) threads = packets ? unsigned(packets) : 1u;
     auto body = [&](unsigned t) {
-        try {
-            Zeroed<LoRaDecoder> dec;
-            dec->setSpreadFactor(c->sf);
-            dec->setSymbolSize(c->ppm);
-            dec->setCodingRate(cr_name(c->rdd));
-            dec->enableWhitening(c->whitening != 0);
-            dec->enableCrcc(c->crc != 0);
-            dec->enableInterleaving(c->interleaving != 0);
-            dec->enableExplicit(c->explicit_header != 0);
-            dec->enableHdr(c->hdr_out != 0);
-            dec->setDataLength(c->data_length);
-            dec->enableErrorCheck(c->error_check != 0);
-            dec->activate();
-            unsigned long long dropped = 0;
-            for (size_t p = packets * t / threads; p < packets * (t + 1) / threads; ++p) {
+        Zeroed<LoRaDecoder> dec;
+        dec->setSpreadFactor(c->sf);
+        dec->setSymbolSize(c->ppm);
+        dec->setCodingRate(cr_name(c->rdd));
+        dec->enableWhitening(c->whitening != 0);
+        dec->enableCrcc(c->crc != 0);
+        dec->enableInterleaving(c->interleaving != 0);
+        dec->enableExplicit(c->explicit_header != 0);
+        dec->enableHdr(c->hdr_out != 0);
+        dec->setDataLength(c->data_length);
+        dec->enableErrorCheck(c->error_check != 0);
+        dec->activate();
+        unsigned long long dropped = 0;
+        for (size_t p = packets * t / threads; p < packets * (t + 1) / threads; ++p) {
+            auto& posted = dec->output(0)->messages;
+            try {
                 Pothos::Packet pkt;
                 pkt.payload = Pothos::BufferChunk(typeid(uint16_t), nsym);
                 std::memcpy(pkt.payload.as<void*>(), symbols + p * symbol_stride, nsym * sizeof(uint16_t));
                 dec->input(0)->pushMessage(Pothos::Object(pkt));
                 dec->work();
-                dec->signals.clear();
-                auto& posted = dec->output(0)->messages;
                 if (dec->getDropped() != dropped) { dropped = dec->getDropped(); n_bytes[p] = -1; }
                 else if (posted.empty()) n_bytes[p] = -2;
                 else {
@@ -178,10 +177,13 @@ extern "C" double pothos_chain_decode_batch(const orc_chain_cfg* c, const uint16
                     if (out) std::memcpy(out + p * payload_stride, r.payload.as<const void*>(),
                                          r.payload.length < payload_stride ? r.payload.length : payload_stride);
                 }
-                posted.clear();
+            } catch (const std::exception&) {
+                // a noise packet whose header announces no CRC and fewer than two bytes makes the block ask for a
+                // (size_t)-wrapped buffer (LoRaDecoder.cpp:381-392): undefined in the reference, an exception here
+                n_bytes[p] = -100;
             }
-        } catch (const std::exception&) {
-            for (size_t p = packets * t / threads; p < packets * (t + 1) / threads; ++p) n_bytes[p] = -100;
+            dec->signals.clear();
+            posted.clear();
         }
     };
     const auto t0 = std::chrono::steady_clock::now();

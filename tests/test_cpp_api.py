@@ -164,7 +164,7 @@ DUMP_FILES = ("payload.bin", "pre_interleave.csv", "post_interleave.csv", "iq_sa
 
 @pytest.mark.gpu
 @pytest.mark.skipif(not (os.path.exists(REF_DUMP) and os.path.exists(OUR_DUMP)), reason="vector dump binaries not built")
-@pytest.mark.parametrize("sf,extra", [(7, []), (8, []), (7, ["--window=hann"]), (9, ["--bytes=33", "--bw=250000"]),
+@pytest.mark.parametrize("sf,extra", [(7, []), (8, []), (7, ["--window=hann"]), (9, ["--bytes=32", "--bw=250000"]),
                                       (12, ["--bytes=5"])])
 def test_vector_dump_stage_files_equal_the_reference(tmp_path, sf, extra):
     """runners/lora_phy_vector_dump.cpp compiled unmodified against this build
@@ -199,17 +199,18 @@ def test_vector_dump_stage_files_equal_the_reference(tmp_path, sf, extra):
 @pytest.mark.gpu
 @needs_runners
 def test_no_alloc_test_report(tmp_path):
-    """tests/no_alloc_test.cpp of the reference, unmodified.  Its guards wrap the FIRST call of lora_modulate /
-    lora_demod_init / lora_demodulate.  In this build the first call for a spreading factor creates the shared device
-    context (host tables, CUDA allocations) -- work the reference does inside the caller-provided workspace -- so the
-    reference's test is expected to stop at its first guard; what must hold is the steady state, which
-    bin/no_alloc_steady checks with the same tracker idea after one warm-up call (zero operator-new calls in
-    modulate / demod_init / demodulate, symbols [0,1,12,34,56] round-trip exactly)."""
+    """tests/no_alloc_test.cpp of the reference, unmodified, must pass against the drop-in (zero allocations seen in
+    lora_modulate / lora_demod_init / lora_demodulate, symbols [0,1,12,34,56] round-trip exactly).  Its tracker is an
+    `inline operator new` in a header, so it sees the allocations of the translation unit it is compiled into; the
+    stricter bin/no_alloc_steady exports a global operator new that also counts what liblora_phy.so,
+    liblora_phy_b200.so and the CUDA runtime inside them allocate: there the first call for a spreading factor
+    creates the shared device context (what the reference's init does inside the caller's workspace; measured: 9
+    allocations in the first lora_modulate, 1 in the first lora_demodulate) and every later call must allocate
+    nothing."""
     exe = os.path.join(PKG, "bin", "ref_no_alloc_test")
     if os.path.exists(exe):
         r = subprocess.run([exe], capture_output=True, text=True)
-        assert "mismatch" not in (r.stdout + r.stderr).lower(), r.stderr
-        assert r.returncode == 0 or "Allocation occurred in modulate" in r.stderr, (r.stdout, r.stderr)
+        assert r.returncode == 0 and "No allocations detected" in r.stdout, (r.stdout, r.stderr)
     steady = os.path.join(PKG, "bin", "no_alloc_steady")
     assert os.path.exists(steady), "bin/no_alloc_steady was not built"
     r = subprocess.run([steady], capture_output=True, text=True)
