@@ -23,6 +23,7 @@
 #include "fft_kernels.h"
 #include "host_tables.h"
 #include "mod_kernels.h"
+#include "scan_kernels.h"
 #include "std_kernels.h"
 #include "stream_kernels.h"
 
@@ -90,10 +91,11 @@ struct lora_b200_ctx {
     Buf h_pin;                   // pinned bounce buffer
     cudaStream_t stream = nullptr;
     // prepass / demod pipeline of large batches: the scan+estimate of sub-batch k+1 runs beside the demod of k
-    cudaStream_t s_pre = nullptr, s_demod = nullptr;
+    cudaStream_t s_pre = nullptr, s_demod = nullptr, s_copy = nullptr;
+    std::vector<cudaEvent_t> ev_h2d;   // one per ingest chunk of the host-buffer receive calls
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     std::vector<cudaEvent_t> ev_pre;
-    int overlap = 0;             // lora_b200_set_overlap (off by default: measured no faster)
+    int overlap = 0;             // lora_b200_set_overlap: scan of sub-batch k+1 beside the demod of sub-batch k (opt-in: measured slower)
     std::mutex mu;
     bool timing = false;                                     // lora_b200_set_kernel_timing
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool; // reused event pairs
@@ -156,6 +158,7 @@ extern "C" int lora_b200_ctx_create(const lora_b200_config* cfg, lora_b200_ctx**
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
         ok = cudaStreamCreateWithPriority(&c->s_pre, cudaStreamNonBlocking, hi) == cudaSuccess &&
              cudaStreamCreateWithPriority(&c->s_demod, cudaStreamNonBlocking, lo) == cudaSuccess &&
+             cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking) == cudaSuccess &&
              cudaEventCreateWithFlags(&c->ev_begin, cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&c->ev_end, cudaEventDisableTiming) == cudaSuccess;
     }
@@ -191,6 +194,8 @@ extern "C" void lora_b200_ctx_destroy(lora_b200_ctx* c)
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->s_pre) cudaStreamDestroy(c->s_pre);
     if (c->s_demod) cudaStreamDestroy(c->s_demod);
+    if (c->s_copy) cudaStreamDestroy(c->s_copy);
+    for (cudaEvent_t e : c->ev_h2d) cudaEventDestroy(e);
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
     for (cudaEvent_t e : c->ev_pre) cudaEventDestroy(e);
@@ -302,10 +307,12 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
         // SF7..SF12: register-blocked kernels (demod_fast.cu).  Batches are cut so that a launch sees < 2^31 windows.
         const int sf = static_cast<int>(c->cfg.sf);
         size_t chunk_packets = total ? std::max<size_t>(1, 0x7fffffffull / total) : n_packets;
-        // Large batches are cut into 8 sub-batches and pipelined over two internal streams: the prepass (a DRAM-bound
-        // scan + two windows per packet) of sub-batch k+1 runs beside the demod kernel (issue-bound) of sub-batch k,
-        // which is launched with one CTA per SM fewer to leave room for it.
-        const bool pipelined = c->overlap && total > 0 && n_packets >= 64 &&
+        // Large legacy batches are cut into 8 sub-batches and pipelined over two internal streams: the normalisation scan
+        // (HBM-bound; scan_kernels.cu, 128 threads x 32 registers per SM) of sub-batch k+1 runs BESIDE the offset
+        // estimate and the demod kernel (fp32-bound, three 256-thread CTAs per SM) of sub-batch k, so the second read
+        // of every sample costs bandwidth the demod kernel leaves idle instead of time.
+        ScanArgs probe{d_iq, packet_stride, count, np, c->n, nullptr, 1.0f, est};
+        const bool pipelined = c->overlap && legacy && total > 0 && n_packets >= 64 && scan_light_supported(probe) &&
                                n_packets * count * sizeof(float2) >= (size_t(256) << 20);
         if (pipelined) chunk_packets = std::min(chunk_packets, (n_packets + 7) / 8);
         const size_t n_sub = (n_packets + chunk_packets - 1) / chunk_packets;
@@ -341,12 +348,16 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             pa.power_scale = c->power_scale;
             pa.est = est + p0;
             pa.tw0 = c->tw0; pa.one = 1.0f;
-            CU(launch_prepass_blocked(sf, pa, st_pre));
-            if (total == 0) continue;
             if (pipelined) {
+                ScanArgs sa{pa.iq, packet_stride, count, pa.n_packets, c->n, dechirp_in ? pa.down : nullptr, 1.0f, est + p0};
+                CU(launch_scan_light(sa, c->sm_count, st_pre));
                 CU(cudaEventRecord(c->ev_pre[sub], st_pre));
                 CU(cudaStreamWaitEvent(st_dem, c->ev_pre[sub], 0));
+                pa.do_maxabs = 0;
+                pa.scale_from_est = 1;
             }
+            CU(launch_prepass_blocked(sf, pa, st_dem));
+            if (total == 0) continue;
 
             BlockedDemodArgs da{};
             da.iq = pa.iq; da.packet_stride = packet_stride; da.count = count;
@@ -370,7 +381,7 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
             da.flag_list = c->flags.as<unsigned>() ? c->flags.as<unsigned>() + 1 : nullptr;
             da.flag_cap = da.n_windows;
             da.stat_rechecked = c->d_stat_rechecked;
-            da.max_ctas_per_sm = pipelined ? 2 : 0;
+            da.max_ctas_per_sm = 0;
             if (c->timing) {
                 if (c->ev_used == c->ev_pool.size()) {
                     cudaEvent_t a = nullptr, b = nullptr;
@@ -809,27 +820,70 @@ extern "C" int lora_b200_modulate_host(lora_b200_ctx* c, const uint16_t* h_symbo
     return LORA_B200_OK;
 }
 
-// demod + chain decode of device-resident IQ, results copied to host buffers; st is synchronised before returning
-static int receive_device_locked(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g, const float2* d_iq,
-                                 size_t n_packets, size_t count, uint8_t* h_payload, lora_b200_chain_result* h_results,
-                                 lora_b200_pkt_metrics* h_metrics, cudaStream_t st)
+// ---- host-buffer receive: chunked, double-buffered ingest ----------------------------
+// The reference's runner reads the whole capture and then calls once (runners/rx_runner.cpp:74-79).  Here a batch of
+// host packets is cut into up to 8 chunks of whole packets (>= 16 MB each): chunk k+1 crosses PCIe on the copy stream
+// (one cudaMemcpyAsync per chunk, source best in pinned memory) while the conversion (int16 / int8 ingest), the demod
+// kernels and the chain decoder of chunk k run on the compute stream; the records of a chunk travel back as soon as
+// it is decoded.  `sample_bytes` = 8 (complex<float>), 4 (int16 I,Q) or 2 (int8 I,Q).
+static int receive_host_chunked(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g, const void* h_iq, int sample_bytes,
+                                float scale, size_t n_packets, size_t count, uint8_t* h_payload,
+                                lora_b200_chain_result* h_results, lora_b200_pkt_metrics* h_metrics)
 {
     const size_t step = static_cast<size_t>(c->n) * c->cfg.osr;
+    if (count / step < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
     const size_t nsym = count / step - 2;
+    const size_t samples = count * n_packets;
+    CU(c->s_iq.reserve(sizeof(float2) * samples));
+    if (sample_bytes != 8) CU(c->s_raw.reserve(static_cast<size_t>(sample_bytes) * samples));
     CU(c->s_sym.reserve(sizeof(uint16_t) * nsym * n_packets + 2));
     CU(c->s_metrics.reserve(sizeof(lora_b200_pkt_metrics) * n_packets));
     CU(c->s_payload.reserve(static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * n_packets));
     CU(c->s_results.reserve(sizeof(lora_b200_chain_result) * n_packets));
-    int rc = demod_batch_locked(c, mode, d_iq, n_packets, count, count, c->s_sym.as<uint16_t>(), nsym,
-                                nullptr, c->s_metrics.as<lora_b200_pkt_metrics>(), st);
-    if (rc) return rc;
-    rc = chain_decode_locked(c, g, c->s_sym.as<uint16_t>(), n_packets, nsym, nsym, c->s_payload.as<uint8_t>(),
-                             c->s_results.as<lora_b200_chain_result>(), st);
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(h_payload, c->s_payload.p, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * n_packets, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(h_results, c->s_results.p, sizeof(lora_b200_chain_result) * n_packets, cudaMemcpyDeviceToHost, st));
-    if (h_metrics)
-        CU(cudaMemcpyAsync(h_metrics, c->s_metrics.p, sizeof(lora_b200_pkt_metrics) * n_packets, cudaMemcpyDeviceToHost, st));
+    CU(c->est.reserve(sizeof(float4) * n_packets));          // sized once: the per-chunk calls must not regrow them
+    CU(c->sync_raw.reserve(sizeof(uint16_t) * 2 * n_packets));
+    if (c->precision == PRECISION_FAST) CU(c->flags.reserve(sizeof(unsigned) * (n_packets * (nsym + 2) + 1)));
+
+    const size_t packet_bytes = count * static_cast<size_t>(sample_bytes);
+    size_t n_chunks = (packet_bytes * n_packets) / (size_t(16) << 20);
+    n_chunks = std::max<size_t>(1, std::min<size_t>(n_chunks, std::min<size_t>(8, n_packets)));
+    const size_t per = (n_packets + n_chunks - 1) / n_chunks;
+    n_chunks = (n_packets + per - 1) / per;
+    while (c->ev_h2d.size() < n_chunks) {
+        cudaEvent_t e = nullptr;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->ev_h2d.push_back(e);
+    }
+    cudaStream_t st = c->stream, cp = c->s_copy;
+    // the staging buffers may still be read by work queued earlier on the compute stream
+    CU(cudaEventRecord(c->ev_begin, st));
+    CU(cudaStreamWaitEvent(cp, c->ev_begin, 0));
+    uint8_t* d_stage = sample_bytes == 8 ? reinterpret_cast<uint8_t*>(c->s_iq.p) : reinterpret_cast<uint8_t*>(c->s_raw.p);
+    for (size_t k = 0; k < n_chunks; ++k) { // every copy is queued up front; the copy engine runs them back to back
+        const size_t p0 = k * per, pn = std::min(per, n_packets - p0);
+        CU(cudaMemcpyAsync(d_stage + p0 * packet_bytes, static_cast<const uint8_t*>(h_iq) + p0 * packet_bytes, pn * packet_bytes,
+                           cudaMemcpyHostToDevice, cp));
+        CU(cudaEventRecord(c->ev_h2d[k], cp));
+    }
+    for (size_t k = 0; k < n_chunks; ++k) {
+        const size_t p0 = k * per, pn = std::min(per, n_packets - p0);
+        CU(cudaStreamWaitEvent(st, c->ev_h2d[k], 0));
+        float2* d_iq = c->s_iq.as<float2>() + p0 * count;
+        if (sample_bytes == 4) CU(launch_convert_i16(c->s_raw.as<short2>() + p0 * count, d_iq, pn * count, scale, c->sm_count, st));
+        if (sample_bytes == 2) CU(launch_convert_i8(c->s_raw.as<char2>() + p0 * count, d_iq, pn * count, scale, c->sm_count, st));
+        uint16_t* d_sym = c->s_sym.as<uint16_t>() + p0 * nsym;
+        lora_b200_pkt_metrics* d_met = c->s_metrics.as<lora_b200_pkt_metrics>() + p0;
+        uint8_t* d_pay = c->s_payload.as<uint8_t>() + p0 * LORA_B200_PAYLOAD_STRIDE;
+        lora_b200_chain_result* d_res = c->s_results.as<lora_b200_chain_result>() + p0;
+        int rc = demod_batch_locked(c, mode, d_iq, pn, count, count, d_sym, nsym, nullptr, d_met, st);
+        if (rc) return rc;
+        rc = chain_decode_locked(c, g, d_sym, pn, nsym, nsym, d_pay, d_res, st);
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(h_payload + p0 * LORA_B200_PAYLOAD_STRIDE, d_pay, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * pn,
+                           cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(h_results + p0, d_res, sizeof(lora_b200_chain_result) * pn, cudaMemcpyDeviceToHost, st));
+        if (h_metrics) CU(cudaMemcpyAsync(h_metrics + p0, d_met, sizeof(lora_b200_pkt_metrics) * pn, cudaMemcpyDeviceToHost, st));
+    }
     CU(cudaStreamSynchronize(st));
     return LORA_B200_OK;
 }
@@ -843,11 +897,7 @@ extern "C" int lora_b200_receive_host(lora_b200_ctx* c, int mode, const lora_b20
     if (n_packets == 0) return LORA_B200_OK;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    if (count / (static_cast<size_t>(c->n) * c->cfg.osr) < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
-    CU(c->s_iq.reserve(sizeof(float2) * count * n_packets));
-    cudaStream_t st = c->stream;
-    CU(cudaMemcpyAsync(c->s_iq.p, h_iq, sizeof(float2) * count * n_packets, cudaMemcpyHostToDevice, st));
-    return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
+    return receive_host_chunked(c, mode, g, h_iq, 8, 1.0f, n_packets, count, h_payload, h_results, h_metrics);
 }
 
 extern "C" int lora_b200_receive_host_i16(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
@@ -859,14 +909,7 @@ extern "C" int lora_b200_receive_host_i16(lora_b200_ctx* c, int mode, const lora
     if (n_packets == 0) return LORA_B200_OK;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    if (count / (static_cast<size_t>(c->n) * c->cfg.osr) < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
-    const size_t samples = count * n_packets;
-    CU(c->s_iq.reserve(sizeof(float2) * samples));
-    CU(c->s_raw.reserve(sizeof(short2) * samples));
-    cudaStream_t st = c->stream;
-    CU(cudaMemcpyAsync(c->s_raw.p, h_iq, sizeof(short2) * samples, cudaMemcpyHostToDevice, st));
-    CU(launch_convert_i16(c->s_raw.as<short2>(), c->s_iq.as<float2>(), samples, scale, c->sm_count, st));
-    return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
+    return receive_host_chunked(c, mode, g, h_iq, 4, scale, n_packets, count, h_payload, h_results, h_metrics);
 }
 
 extern "C" int lora_b200_receive_host_i8(lora_b200_ctx* c, int mode, const lora_b200_chain_cfg* g,
@@ -878,14 +921,7 @@ extern "C" int lora_b200_receive_host_i8(lora_b200_ctx* c, int mode, const lora_
     if (n_packets == 0) return LORA_B200_OK;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    if (count / (static_cast<size_t>(c->n) * c->cfg.osr) < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
-    const size_t samples = count * n_packets;
-    CU(c->s_iq.reserve(sizeof(float2) * samples));
-    CU(c->s_raw.reserve(sizeof(char2) * samples));
-    cudaStream_t st = c->stream;
-    CU(cudaMemcpyAsync(c->s_raw.p, h_iq, sizeof(char2) * samples, cudaMemcpyHostToDevice, st));
-    CU(launch_convert_i8(c->s_raw.as<char2>(), c->s_iq.as<float2>(), samples, scale, c->sm_count, st));
-    return receive_device_locked(c, mode, g, c->s_iq.as<float2>(), n_packets, count, h_payload, h_results, h_metrics, st);
+    return receive_host_chunked(c, mode, g, h_iq, 2, scale, n_packets, count, h_payload, h_results, h_metrics);
 }
 
 // ---- small host-buffer entry points used by include/lora_phy/phy.hpp -------------------------------------------

@@ -145,8 +145,19 @@ struct DemodCfg {
     static constexpr int SMEM_C64 = SLOTS * Blk<SF>::WIN;
 };
 
+// A/B switches (scripts/ab_build.sh -D...): LORA_V_PREFETCH = the fused flavour keeps the NEXT window's samples of a
+// run in registers (loads issued a whole window ahead; 2 CTAs/SM at <= 128 registers instead of 3 at 80).
+#ifndef LORA_V_PREFETCH
+#define LORA_V_PREFETCH 0
+#endif
+// Resident CTAs per SM of the fused flavour.  Measured on one box (profiles/r2_ab_kernel_variants.txt): two CTAs with up
+// to 128 registers beat three with 80 at SF7-SF10 (+4.6 / +3.1 / +4.3 / +2.6 %: no spills, the stage geometry stays in
+// registers) and lose at SF11 / SF12 (-1 / -6 %: one window per CTA there, so a third CTA is a third independent phase).
+#ifndef LORA_V_CTAS
+#define LORA_V_CTAS(SF) (LORA_V_PREFETCH ? 2 : ((SF) <= 10 ? 2 : 3))
+#endif
 template <int SF, bool FAITH, bool LIST, bool OSR1>
-__global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
+__global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
 {
     using B = Blk<SF>;
     constexpr int N = B::N, T = B::T, SLOTS = DemodCfg<SF>::SLOTS;
@@ -176,6 +187,8 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
         const float peak_scale = pk_.scale * pk_.scale;
         int rot_ofs = -1;
         c64 rot[16];
+        c64 nxt[LORA_V_PREFETCH ? 16 : 1];
+        bool have_nxt = false;
         for (; s < s_end; ++s) {
             const WinParams q = window_params<SF, FAITH, OSR1>(a, pk_, s);
             const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
@@ -186,13 +199,26 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : 3) demod_blocked_kernel(cons
                 l2_prefetch(x + span, sizeof(c64) * min(span, left));
             }
             c64 in[16], v[16];
-            if (OSR1) {
+            constexpr bool PF = LORA_V_PREFETCH && !FAITH && !LIST && OSR1;
+            if (PF && have_nxt) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) in[j] = nxt[j];
+            } else if (OSR1) {
                 const c64* xt = x + t;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) in[j] = __ldg(xt + T * j);
             } else {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
+            }
+            if (PF) { // the next window of this run: its loads travel while this window is transformed
+                have_nxt = s + 1 < s_end;
+                if (have_nxt) {
+                    const WinParams qn = window_params<SF, FAITH, OSR1>(a, pk_, s + 1);
+                    const c64* xn = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + qn.base + t;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) nxt[j] = __ldg(xn + T * j);
+                }
             }
             float margin = 0.0f;
             if (FAITH) {
@@ -273,7 +299,8 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
     const int p = blockIdx.x * SLOTS + slot;
     if (p >= a.n_packets) return; // whole slots leave together; slots never synchronise with each other
     const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride;
-    float4 e = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+    // scale_from_est: the light scan kernel (scan_kernels.cu) already wrote scale and max_amp for this packet
+    float4 e = a.scale_from_est ? a.est[p] : make_float4(0.0f, 0.0f, 1.0f, 0.0f);
 
     // LoRaDemod.cpp:59-77: max over all samples of max(|re|,|im|), comparisons written so a NaN never wins.
     // In fused-dechirp mode the values examined are iq * down[n mod N] (performance_test.cpp:109-114).

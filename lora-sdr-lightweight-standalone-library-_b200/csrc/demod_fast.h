@@ -60,6 +60,7 @@ struct PrepassArgs {
     size_t packet_stride, count;
     int n_packets;
     int do_maxabs;     // legacy modes: LoRaDemod.cpp:59-77
+    int scale_from_est; // the scan already ran (scan_kernels.cu): take est[p].z / .w from memory instead
     int symbols;       // windows to estimate over (min(total, 2) inside demodulate; all of them for estimate_offsets)
     int osr;
     int dechirp;       // multiply by the down-chirp first (fused caller-dechirp only)

@@ -26,6 +26,11 @@
 
 #include "packed_math.cuh"
 
+// A/B switch: the fused flavour derives w^2k, w^3k from w^k for SF >= this value (13 = never)
+#ifndef LORA_V_DERIVE_FROM
+#define LORA_V_DERIVE_FROM 11
+#endif
+
 namespace lora_b200 {
 
 template <int SF>
@@ -162,7 +167,7 @@ PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restric
                         // Fused flavour, SF >= 11: w^2k and w^3k from w^k (4 packed instructions instead of two
                         // loads).  Measured +5 % / +3 % at SF11 / SF12, where load latency binds, and -1 ... -3 % at
                         // SF9 / SF10 (deriving only w^3k: +-1 % everywhere); the extra 1e-7 relative error is far inside the margin of the argmax filter.
-                        if (FAITH || SF < 11) { w2 = __ldg(wp + B::m(s)); w3 = __ldg(wp + 2 * B::m(s)); }
+                        if (FAITH || SF < LORA_V_DERIVE_FROM) { w2 = __ldg(wp + B::m(s)); w3 = __ldg(wp + 2 * B::m(s)); }
                         else {
                             w2 = cmul<false>(w1, w1, one);
                             w3 = cmul<false>(w2, w1, one);

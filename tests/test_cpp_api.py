@@ -165,7 +165,7 @@ DUMP_FILES = ("payload.bin", "pre_interleave.csv", "post_interleave.csv", "iq_sa
 @pytest.mark.gpu
 @pytest.mark.skipif(not (os.path.exists(REF_DUMP) and os.path.exists(OUR_DUMP)), reason="vector dump binaries not built")
 @pytest.mark.parametrize("sf,extra", [(7, []), (8, []), (7, ["--window=hann"]), (9, ["--bytes=32", "--bw=250000"]),
-                                      (12, ["--bytes=5"])])
+                                      (12, ["--bytes=4"])])
 def test_vector_dump_stage_files_equal_the_reference(tmp_path, sf, extra):
     """runners/lora_phy_vector_dump.cpp compiled unmodified against this build
     (encode -> modulate -> demodulate on the GPU, the code helpers from this build's LoRaCodes.hpp) writes the seven

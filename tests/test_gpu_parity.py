@@ -439,3 +439,84 @@ def test_stream_pipelined_sub_batches_give_the_same_results(env):
         out.append((rx.clone(), met.clone(), pk.clone()))
     for a, b in zip(*out):
         assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf,mode_name", [(7, "dechirp"), (9, "dechirp"), (9, "legacy"), (12, "dechirp")])
+def test_overlapped_scan_equals_two_pass_path(env, sf, mode_name):
+    """Large legacy batches run the normalisation scan of sub-batch k+1 (csrc/scan_kernels.cu: bulk-copy staged, a
+    floating-point filter in front of the reference's comparisons) beside the demod kernel of sub-batch k.  Symbols,
+    sync words, cfo, time offset and max_amp must equal the single-stream path bit for bit, including packets that are
+    all zero, carry NaN / Inf (LoRaDemod.cpp:59-77 compares, it does not call fmax), have their largest component far
+    above the rest, or -- plain legacy mode -- end in a ragged tail with an odd sample count."""
+    torch, L = env["torch"], env["L"]
+    n = 1 << sf
+    mode = L.DEMOD_LEGACY_DECHIRP if mode_name == "dechirp" else L.DEMOD_LEGACY
+    nsym = 24
+    count = (nsym + 2) * n + (0 if mode_name == "dechirp" else n // 2 + 1)       # odd, ragged in legacy mode
+    packets = max(64, -(-(300 << 20) // (count * 8)))                             # >= 256 MB so the call pipelines
+    ctx = L.Context(sf)
+    g = torch.Generator(device="cuda").manual_seed(sf)
+    sym = torch.randint(0, n, (packets, nsym), dtype=torch.int16, device="cuda", generator=g)
+    iq = torch.zeros((packets, count + (count & 1)), dtype=torch.complex64, device="cuda")[:, :count]
+    iq[:, :(nsym + 2) * n] = ctx.modulate_batch(sym)
+    snr = (torch.rand(packets, device="cuda", generator=g) * 30.0 - 20.0).float().contiguous()
+    ctx.awgn_batch(iq, snr, seed=sf)
+    iq[1] = 0                                                                    # all-zero packet
+    iq[2, 3 * n + 5] = complex(float("nan"), 50.0)                               # NaN real part drops the sample
+    iq[3, 4 * n + 9] = complex(40.0, float("nan"))                               # NaN imaginary part only itself
+    iq[4, 7 * n] = complex(1.0, float("-inf"))
+    iq[5] *= 1e-3; iq[5, count - 1] = complex(0.0, -77.0)                         # the very last sample decides
+    iq[6] *= 0.01                                                                 # never normalised (max < 1)
+    iq[7] *= 1e20; iq[8] *= 1e-25                                                 # |x|^2 overflows / underflows in float
+    assert iq.stride(0) % 2 == 0 and iq.data_ptr() % 16 == 0
+    out = {}
+    for overlap in (0, 1):
+        ctx.set_overlap(overlap)
+        s, m, pk = ctx.demod_batch(iq, mode=mode, want_peaks=True)
+        torch.cuda.synchronize()
+        out[overlap] = (s.cpu().numpy().copy(), m.cpu().numpy().copy(), pk.cpu().numpy().copy())
+    ctx.set_overlap(1)
+    assert bits(out[0][1]) == bits(out[1][1]), "metrics (cfo, time offset, max_amp, sync) differ"
+    assert bits(out[0][0]) == bits(out[1][0]), "symbols differ"
+    a, b = out[0][2], out[1][2]
+    assert ((a == b) | (np.isnan(a) & np.isnan(b))).all(), "peaks differ"
+    met = out[1][1].view(L.PKT_METRICS).reshape(-1)
+    assert met["max_amp"][1] == 0 and np.isinf(met["max_amp"][4]) and met["max_amp"][5] == 77.0 and met["max_amp"][3] >= 40.0
+    assert met["normalised"][6] == 0 and met["normalised"][0] == 1
+
+
+@pytest.mark.gpu
+def test_chunked_host_receive_equals_device_path(env):
+    """SURVEY 8(f) rank 2, second half: lora_b200_receive_host* cut the batch into chunks whose PCIe copy overlaps the
+    kernels of the chunk before (csrc/capi.cu receive_host_chunked).  With enough bytes for several chunks (and a packet
+    count that does not divide evenly) payloads, results and metrics must equal the device-resident calls bit for bit,
+    for float32, int16 and int8 samples, from pinned and from pageable host memory."""
+    torch, L = env["torch"], env["L"]
+    sf, packets = 9, 5003                                        # 5003 x 35 x 512 x 8 B = 717 MB: eight ragged chunks
+    ctx = L.Context(sf)
+    cfg = L.chain_cfg(sf, 1)
+    gen = torch.Generator(device="cuda").manual_seed(77)
+    pay = torch.randint(0, 256, (packets, 16), dtype=torch.uint8, device="cuda", generator=gen)
+    iq = ctx.modulate_batch(ctx.chain_encode_batch(cfg, pay), amplitude=0.25)
+    ctx.awgn_batch(iq, (torch.rand(packets, device="cuda", generator=gen) * 25.0 - 5.0).float().contiguous(), seed=3)
+    q16 = torch.view_as_real(iq).mul(8192.0).round_().clamp_(-32768, 32767).to(torch.int16)
+    q8 = torch.view_as_real(iq).mul(96.0).round_().clamp_(-128, 127).to(torch.int8)
+    for name, host, dev in (("f32", iq, iq),
+                            ("i16", q16, torch.view_as_complex(q16.float().mul(1.0 / 32768.0).contiguous())),
+                            ("i8", q8, torch.view_as_complex(q8.float().mul(1.0 / 128.0).contiguous()))):
+        rx, met, _ = ctx.demod_batch(dev.contiguous(), mode=L.DEMOD_LEGACY_DECHIRP)
+        out, res = ctx.chain_decode_batch(cfg, rx.contiguous())
+        want = (out.cpu().numpy(), res.cpu().numpy(), met.cpu().numpy())
+        for pinned in (True, False):
+            h = torch.empty(host.shape, dtype=host.dtype, pin_memory=pinned)
+            h.copy_(host)
+            hn = h.numpy()
+            if name == "f32":
+                p, r, m = ctx.receive_host(cfg, hn)
+            elif name == "i16":
+                p, r, m = ctx.receive_host_i16(cfg, hn)
+            else:
+                p, r, m = ctx.receive_host_i8(cfg, hn)
+            assert bits(p) == bits(want[0]) and bits(r) == bits(want[1]) and bits(m) == bits(want[2]), (name, pinned)
+    assert (want[1].view(L.CHAIN_RESULT)["crc_ok"] == 1).mean() > 0.5
