@@ -151,7 +151,7 @@ class Workload:
                 metrics=torch.zeros((n, 16), dtype=torch.uint8, device="cuda"),
                 out=torch.zeros((n, L.PAYLOAD_STRIDE), dtype=torch.uint8, device="cuda"),
                 results=torch.zeros((n, 16), dtype=torch.uint8, device="cuda"),
-                windows=n * (nsym + 2), samples=n * (nsym + 2) * (1 << sf)))
+                nsym=nsym, windows=n * (nsym + 2), samples=n * (nsym + 2) * (1 << sf)))
         torch.cuda.synchronize()
         self.samples = sum(i["samples"] for i in self.items)
         self.windows = sum(i["windows"] for i in self.items)
@@ -354,6 +354,87 @@ def run_reference(args, rank):
         "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+def bind_to_gpu_numa_node(local):
+    """Pin this rank's host threads to the CPUs of the NUMA node its GPU hangs off (sysfs: the GPU's PCI device ->
+    numa_node -> cpulist), so the pinned staging buffers it allocates next are first-touched on that node and the H2D
+    copies of eight ranks do not all pull from node 0 (round 1: per-GPU end-to-end rate fell 2.3x from N=2 to N=8).
+    -> a small record for the JSON line; does nothing (and says so) where sysfs has no answer or there is one node."""
+    info = {"numa_node": None, "cpus": None, "bound": False}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = local
+        if visible:
+            ids = [v.strip() for v in visible.split(",") if v.strip()]
+            if local < len(ids) and ids[local].isdigit():
+                phys = int(ids[local])
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(phys)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]                       # sysfs uses a 4-digit PCI domain
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        info["numa_node"] = node
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        if node < 0 or len(nodes) < 2:
+            return info
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info.update(cpus=len(cpus), bound=True)
+    except Exception as e:  # best effort: a box without sysfs / NVML just runs unbound
+        info["error"] = repr(e)[:120]
+    return info
+
+
+def run_extras(args, torch, L, dist, rank, world):
+    """configs[3] (continuous-stream scan) and configs[4] (multi-channel gateway) as short legs after the headline, so
+    the driver's record carries them at every N.  Both are strong scaling: the input set is fixed and split over ranks."""
+    import contextlib
+    import types
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    out = {}
+    try:
+        import profile_stream
+        n_streams = 4096 // world
+        with contextlib.redirect_stdout(sys.stderr):   # the script narrates; this program prints ONE JSON line
+            rep = profile_stream.config3(types.SimpleNamespace(streams=n_streams, length=1 << 18, reps=2))
+        ms = torch.tensor([rep["all_detectors_ms"]], dtype=torch.float64, device="cuda")
+        cnt = torch.tensor([sum(v["frames_snr_ge_0dB"] for v in rep["per_sf"].values()),
+                            sum(v["detected"] for v in rep["per_sf"].values()), rep["false_packets"]],
+                           dtype=torch.int64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(cnt)
+        pk, _ = peaks()
+        samples = rep["samples"] * world
+        t = float(ms.item())
+        rep.update(streams=n_streams * world, samples=samples, all_detectors_ms=round(t, 3), value=samples / t / 1e3,
+                   p_detect_snr_ge_0dB=int(cnt[1]) / max(int(cnt[0]), 1), false_packets=int(cnt[2]), n_gpus=world,
+                   scaling="strong",
+                   roofline={"bound": "hbm", "unit": "GB/s", "peak": pk["hbm_gbs"],
+                             "algorithmic_bytes": 8 * samples * 4, "note": "each of the four synchronisers reads every sample once",
+                             "achieved": 8 * samples * 4 / world / t / 1e6, "frac": 8 * samples * 4 / world / t / 1e6 / pk["hbm_gbs"]})
+        rep["per_sf"] = {k: v for k, v in rep["per_sf"].items()} if rank == 0 else {}
+        out["stream"] = rep
+    except Exception as e:
+        out["stream"] = {"error": repr(e)[:300]}
+    torch.cuda.empty_cache()
+    try:
+        import gateway
+        g = gateway.run(types.SimpleNamespace(channels=4096, sf12_packets=4, steps=max(args.steps, 3), warmup=3, graph=False),
+                        rank, world, dist)
+        out["gateway"] = g
+    except Exception as e:
+        out["gateway"] = {"error": repr(e)[:300]}
+    torch.cuda.empty_cache()
+    return out
+
+
 # ---- this repo's arm ---------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -368,6 +449,7 @@ def main():
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace"])
     ap.add_argument("--no-int16", action="store_true", help="skip the extra int16-ingest end-to-end leg")
     ap.add_argument("--no-perf-test", action="store_true", help="skip the reference's own performance_test / rx_runner runs")
+    ap.add_argument("--no-extras", action="store_true", help="skip the configs[3] stream scan and configs[4] gateway legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -377,9 +459,10 @@ def main():
         return
     args.warmup = max(args.warmup, 3)
 
+    numa = bind_to_gpu_numa_node(local)
     import torch
     import lora_phy_b200 as L
-    from lora_phy_b200.shard import gather_records
+    from lora_phy_b200.shard import gather_records_to_root
     assert torch.cuda.is_available(), "bench.py needs a CUDA device; there is no CPU fallback"
     torch.cuda.set_device(local)
     dist = None
@@ -402,17 +485,17 @@ def main():
     REC = 272
     if dist is not None:
         res_cat = torch.zeros((len(SFS) * packets, REC), dtype=torch.uint8, device="cuda")
-        gather_buf = torch.zeros((world * len(SFS) * packets, REC), dtype=torch.uint8, device="cuda")
+        gather_buf = torch.zeros((world * len(SFS) * packets, REC), dtype=torch.uint8, device="cuda") if rank == 0 else None
 
     def one_step():
         wl.step(mode)
-        if dist is not None:  # the only NVLink traffic: one all-gather of the decoded records
+        if dist is not None:  # the only NVLink traffic: the decoded records travel once, to the forwarding rank
             for k, i in enumerate(wl.items):
                 rows = res_cat[k * packets:(k + 1) * packets]
                 rows[:, 0:16] = i["results"]
                 rows[:, 16:32] = i["metrics"]
                 rows[:, 32:REC] = i["out"][:, :REC - 32]
-            gather_records(res_cat, dist, out=gather_buf)
+            gather_records_to_root(res_cat, dist, root=0, out=gather_buf)
 
     for _ in range(args.warmup):
         one_step()
@@ -479,6 +562,7 @@ def main():
     e2e = {"value": e_samples * world * args.steps / dt / 1e6, "unit": "Msamples/s",
            "h2d_bytes_per_step": int(e_samples * 8) * world,
            "d2h_bytes_per_step": int(sum(p.nbytes + r.nbytes + m.nbytes for _, _, p, r, m, _ in pinned)) * world,
+           "h2d_GBps_per_gpu": e_samples * 8 * args.steps / dt / 1e9,
            "sample": f"{pe} packets per SF per GPU through lora_b200_receive_host, pinned host buffers"}
 
     # the same end-to-end leg with int16 I/Q samples: half the PCIe bytes.  Reported
@@ -511,6 +595,15 @@ def main():
                    "h2d_bytes_per_step": int(e_samples * 4) * world, "crc_ok_packets_rank0": ok16,
                    "call": "lora_b200_receive_host_i16 (int16 I/Q, scale 2^-11), same packets quantised"}
         del i16
+
+    # what the CPU cross-check needs from the device, then the 100+ GB of inputs make room for the extra legs
+    for i in wl.items:
+        i["results_h"] = i["results"][:pe].cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)
+        i["out_h"] = i["out"][:pe, :PAYLOAD_LEN].cpu().numpy()
+        for k in ("iq", "rx", "tx_full", "out", "results", "metrics", "payload", "snr"):
+            i.pop(k, None)
+    torch.cuda.empty_cache()
+    extras = None if args.no_extras else run_extras(args, torch, L, dist, rank, world)
 
     if rank != 0:
         if dist is not None:
@@ -559,7 +652,7 @@ def main():
         try:
             pc = min(args.cpu_packets, pe)
             threads = os.cpu_count() or 1
-            host_items = [(i["sf"], h_iq[:pc], i["tx"].shape[1]) for i, h_iq, _, _, _, _ in pinned]
+            host_items = [(i["sf"], h_iq[:pc], i["nsym"]) for i, h_iq, _, _, _, _ in pinned]
             cpu_reference_time([(sf, iq[:64], n) for sf, iq, n in host_items], threads)          # warm the pages and threads
             dt_c, s_c, kind, ok_cpu = cpu_reference_time(host_items, threads)
             # live parity check on this sample: the packets the reference's CPU code (unmodified lora_demodulate +
@@ -567,11 +660,11 @@ def main():
             ok_gpu, differ = 0, 0
             last = getattr(cpu_reference_time, "last", [])
             for k, i in enumerate(wl.items):
-                r = i["results"][:pc].cpu().numpy().view(L.CHAIN_RESULT).reshape(-1)
+                r = i["results_h"][:pc]
                 ok_gpu += int((r["n_bytes"] == PAYLOAD_LEN).sum())
                 if k < len(last):
                     nb, out = last[k]
-                    g_out = i["out"][:pc, :PAYLOAD_LEN].cpu().numpy()
+                    g_out = i["out_h"][:pc]
                     both = (nb >= 0) & (r["n_bytes"] >= 0)
                     differ += int(((nb >= 0) != (r["n_bytes"] >= 0)).sum()) + int((nb[both] != r["n_bytes"][both]).sum())
                     same_len = both & (nb == PAYLOAD_LEN) & (r["n_bytes"] == PAYLOAD_LEN)
@@ -595,7 +688,7 @@ def main():
         "config": {"workload": "configs[1]: SF7-SF12 sweep, synthetic AWGN -20..+10 dB, demod + full decode",
                    "packets_per_sf_per_gpu": packets, "payload_bytes": PAYLOAD_LEN, "cr": "4/5",
                    "header": "explicit", "crc": True, "bw_hz": 125000, "osr": 1,
-                   "demod_semantics": args.mode, "parallelism": f"{world} independent shards, no data-path collective; one all-gather of 272-byte decoded records per step",
+                   "demod_semantics": args.mode, "parallelism": f"{world} independent shards, no data-path collective; one gather of 272-byte decoded records to rank 0 per step",
                    "l2": "inputs (>= 2.3 GB per batch) are larger than the 126 MB L2; no flush needed",
                    "per_sf": per_sf_out},
         "clocks": clock_info, "gpu_launches": int(launches),
@@ -617,6 +710,9 @@ def main():
     if e2e_i16:
         line["e2e_int16"] = e2e_i16
     line["cpu_baseline"] = cpu
+    line["host"] = {"numa": numa, "cpus": os.cpu_count()}
+    if extras is not None:
+        line["extra"] = extras
     if cpu_error:
         line["cpu_error"] = cpu_error
     print(json.dumps(line))

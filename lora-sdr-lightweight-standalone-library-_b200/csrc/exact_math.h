@@ -10,7 +10,8 @@
 // optimized-routines sincosf with its double-precision polynomials, and the fdlibm float
 // atanf/atan2f) with every floating-point operation spelled out un-fused, so that the CUDA build
 // (IEEE double/float, no FMA contraction) and a plain C build produce identical bits.  The C build
-// of this same header is compared against the host libm in tests/test_exact_math.py.
+// of this same header is compared against the host libm by scripts/check_exact_math.c (run, in its sampled mode,
+// by tests/test_exact_math.py).
 //
 // Everything here is a pure function of its argument: no tables in memory except the 2/pi digits.
 #pragma once
@@ -222,6 +223,56 @@ XM_HD void xm_sincosf(float y, float* s, float* c)
     xm_reduce(y, &xr, &x2, &odd, &neg);
     *s = xm_sincos_poly(xr, x2, odd, neg);
     *c = xm_sincos_poly(xr, x2, odd ^ 1, neg);
+}
+
+// Branch-free form of xm_sincosf for code that evaluates several arguments side by side (the chirp modulator
+// interleaves four): both range reductions are computed and one is selected, each polynomial is evaluated exactly
+// once and sine / cosine pick theirs, so there is no divergent path for a scheduler to serialise.  Same bits as
+// xm_sincosf for every float (scripts/check_exact_math.c).  Why the separate |y| < pi/4 path of xm_sincosf is not
+// needed: there the fast reduction yields n = 0 and fma(-0, pi/2, x) = x exactly, i.e. the same polynomial inputs.
+XM_HD void xm_sincosf_bf(float y, float* s, float* c)
+{
+    const uint32_t bits = xm_f2u(y);
+    const uint32_t top = (bits >> 20) & 0x7ffu;
+    const double x = (double)y;
+    // |y| < 120: one multiply and one fused multiply-subtract
+    const double r = XM_DMUL(x, XM_HPI_INV_2P24);
+#if defined(__CUDA_ARCH__)
+    const int32_t ri = __double2int_rz(r); // saturates for arguments the selection below discards
+#else
+    const int32_t ri = (r > -2.0e9 && r < 2.0e9) ? (int32_t)r : 0;
+#endif
+    const int ns = (ri + 0x800000) >> 24;
+    const double xs = XM_DFMA(-(double)ns, XM_HPI, x);
+    // |y| >= 120: 24-bit mantissa times 96 bits of 2/pi
+    const int sign = (int)(bits >> 31);
+    const int base = (int)((bits >> 26) & 15u);
+    const int shift = (int)((bits >> 23) & 7u);
+    uint32_t xi = (bits & 0xffffffu) | 0x800000u;
+    xi <<= shift;
+    uint64_t res0 = (uint64_t)(uint32_t)(xi * xm_inv_pio4(base));
+    const uint64_t res1 = (uint64_t)xi * xm_inv_pio4(base + 4);
+    const uint64_t res2 = (uint64_t)xi * xm_inv_pio4(base + 8);
+    res0 = (res2 >> 32) | (res0 << 32);
+    res0 += res1;
+    const uint64_t nn = (res0 + (1ull << 61)) >> 62;
+    res0 -= nn << 62;
+    const double xl = XM_DMUL((double)(int64_t)res0, XM_PI63);
+    const int big = top >= ((0x42f00000u >> 20) & 0x7ffu);
+    const double xx = big ? xl : xs;
+    const int n = big ? (int)nn : ns;
+    const int q = big ? ((n + sign) & 3) : (n & 3);
+    const double sgn = (q == 1 || q == 2) ? -1.0 : 1.0;
+    const int neg = (q & 2) != 0, odd = n & 1;
+    const double x2 = XM_DMUL(xx, xx);
+    const double xr = XM_DMUL(xx, sgn);
+    const float ps = xm_sincos_poly(xr, x2, 0, 0);   // sine polynomial
+    const float pc = xm_sincos_poly(xr, x2, 1, neg); // cosine polynomial, sign applied
+    float sv = odd ? pc : ps, cv = odd ? ps : pc;
+    if (top < ((0x39800000u >> 20) & 0x7ffu)) { sv = y; cv = 1.0f; } // |y| < 2^-12
+    if (top >= 0x7f8u) { sv = y - y; cv = y - y; }                    // inf / nan
+    *s = sv;
+    *c = cv;
 }
 
 // ---- atanf / atan2f (fdlibm float algorithm as shipped in glibc 2.39) ------------------------------

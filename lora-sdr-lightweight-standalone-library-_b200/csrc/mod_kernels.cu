@@ -10,16 +10,29 @@ namespace lora_b200 {
 // genChirp (include/lora_phy/ChirpGenerator.hpp:24-50) is a serial float recurrence over every sample of a
 // packet: f += fStep (wrapped at fMax), phase += f, and the phase is carried from symbol to symbol
 // (LoRaMod.cpp:13,25-41) with one double-precision wrap per symbol (:48).  Float addition is not
-// associative, so only packet-level parallelism reproduces it.  Layout: a warp owns 32 packets; each lane
-// runs its packet's recurrence for CHUNK samples into shared memory (2 dependent float adds per sample),
-// then the whole warp turns each packet's CHUNK phases into (ampl*cos, ampl*sin) -- the expensive part --
-// with lanes across consecutive samples, so the stores are full 256-byte lines.
+// associative, so only packet-level parallelism reproduces it.  Layout: a warp owns 32 packets and walks them in
+// chunks of 32 samples.
+//   * Recurrence: lane l advances packet l, two dependent float adds per sample -- a latency chain, not work.  It
+//     runs ONE CHUNK AHEAD, interleaved step by step with the evaluation below (double-buffered in shared memory),
+//     so its latency is hidden behind the expensive part instead of preceding it.
+//   * Evaluation: phases -> (ampl*cos, ampl*sin) with glibc's cosf/sinf bits (exact_math.h, double-precision
+//     polynomials), lanes across the 32 consecutive samples of one packet so every store is a full 256-byte line.
+//     Four packets are evaluated side by side with the branch-free xm_sincosf_bf: four independent dependency
+//     chains per thread, because with one lane per packet a batch of P packets only ever has P/32 warps to hide
+//     latency with (14 per SM at 65,536 packets).
+// Algorithmic bytes: 8*N*osr written per symbol (+2 read); bound: issue slots of the fp64-exact sincos (~70
+// instructions per sample), about 0.6 of the HBM write roofline.
 constexpr int MOD_CHUNK = 32;
 constexpr int MOD_WARPS = 4;
 
+struct ChirpState { // one packet's genChirp / lora_modulate state, held by one lane
+    float f, phase;
+    int s, j;       // symbol index (sync words first) and sample index inside it
+};
+
 __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a)
 {
-    __shared__ float ph[MOD_WARPS][32][MOD_CHUNK + 1];
+    __shared__ float ph[MOD_WARPS][2][32][MOD_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pk0 = (blockIdx.x * MOD_WARPS + warp) * 32;
     if (pk0 >= a.n_packets) return; // whole warp
@@ -38,35 +51,54 @@ __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a
     const uint16_t* sym = a.symbols + (size_t)(live ? pk : pk0) * a.symbol_stride;
     const int total = (int)a.n_symbols + 2;
     const int warp_live = min(32, a.n_packets - pk0);
+    const size_t n_samples = (size_t)total * step;
+    const size_t n_chunks = (n_samples + MOD_CHUNK - 1) / MOD_CHUNK;
 
-    float phase = 0.0f; // LoRaMod.cpp:13
-    for (int s = 0; s < total; ++s) {
-        const unsigned v = s == 0 ? a.sw0 : s == 1 ? a.sw1 : (unsigned)sym[s - 2];
-        // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
-        const float f0 = __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom);
-        float f = __fadd_rn(f_min, f0);
-        for (int c0 = 0; c0 < step; c0 += MOD_CHUNK) {
-            const int len = min(MOD_CHUNK, step - c0);
-            for (int j = 0; j < len; ++j) { // ChirpGenerator.hpp:41-45 (up-chirp branch)
-                f = __fadd_rn(f, f_step);
-                if (f > f_max) f = __fsub_rn(f, span);
-                phase = __fadd_rn(phase, f);
-                ph[warp][lane][j] = phase;
-            }
-            __syncwarp();
-            for (int q = 0; q < warp_live; ++q) {
-                if (lane < len) {
-                    float sn, cs;
-                    xm_sincosf(ph[warp][q][lane], &sn, &cs); // std::polar -> cosf/sinf
-                    a.iq[(size_t)(pk0 + q) * a.packet_stride + (size_t)s * step + c0 + lane] =
-                        make_float2(__fmul_rn(a.amplitude, cs), __fmul_rn(a.amplitude, sn));
-                }
-            }
-            __syncwarp();
+    ChirpState st{0.0f, 0.0f, 0, 0}; // LoRaMod.cpp:13: phase = 0
+    // One step of the recurrence: the phase of the next sample of this lane's packet (any value past the packet's end).
+    auto next_phase = [&]() -> float {
+        if (st.s >= total) return 0.0f;
+        if (st.j == 0) {
+            const unsigned v = st.s == 0 ? a.sw0 : st.s == 1 ? a.sw1 : (unsigned)sym[st.s - 2];
+            // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
+            const float f0 = __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom);
+            st.f = __fadd_rn(f_min, f0);
         }
-        // :48 -- wrap once per chirp, in double, narrowed back into the float accumulator
-        const double pd = (double)phase;
-        phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
+        st.f = __fadd_rn(st.f, f_step);                 // ChirpGenerator.hpp:41-45 (up-chirp branch)
+        if (st.f > f_max) st.f = __fsub_rn(st.f, span);
+        st.phase = __fadd_rn(st.phase, st.f);
+        const float out = st.phase;
+        if (++st.j == step) { // :48 -- wrap once per chirp, in double, narrowed back into the float accumulator
+            const double pd = (double)st.phase;
+            st.phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
+            st.j = 0;
+            ++st.s;
+        }
+        return out;
+    };
+
+    for (int j = 0; j < MOD_CHUNK; ++j) ph[warp][0][lane][j] = next_phase();
+    for (size_t k = 0; k < n_chunks; ++k) {
+        __syncwarp();
+        const float(*cur)[MOD_CHUNK + 1] = ph[warp][k & 1];
+        float(*nxt)[MOD_CHUNK + 1] = ph[warp][(k + 1) & 1];
+        const size_t at = k * MOD_CHUNK + lane;           // this lane's sample in every packet of the warp
+        const bool in_range = at < n_samples;
+#pragma unroll 1
+        for (int q = 0; q < 32; q += 4) {
+            float y[4], sn[4], cs[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) y[i] = cur[q + i][lane];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) nxt[lane][q + i] = next_phase(); // the recurrence, one chunk ahead
+#pragma unroll
+            for (int i = 0; i < 4; ++i) xm_sincosf_bf(y[i], &sn[i], &cs[i]); // std::polar -> cosf/sinf
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (in_range && q + i < warp_live)
+                    a.iq[(size_t)(pk0 + q + i) * a.packet_stride + at] =
+                        make_float2(__fmul_rn(a.amplitude, cs[i]), __fmul_rn(a.amplitude, sn[i]));
+        }
     }
 }
 

@@ -1,8 +1,9 @@
 """Multi-GPU plumbing of the receive path: which rank owns which channel, and the one collective of a step.
 
 Packets / channels / streams are independent: every rank demodulates and decodes its own
-share with no data-path collective, and only the fixed-stride decoded records cross NVLink -- one
-all_gather_into_tensor per step (NCCL on GPUs; the same code runs on gloo with CPU tensors in the tests).
+share with no data-path collective, and only the fixed-stride decoded records cross NVLink -- one gather to the
+forwarding rank per step (or an all-gather where every rank wants them; NCCL on GPUs, the same code runs on gloo with
+CPU tensors in the tests).
 """
 
 
@@ -39,6 +40,23 @@ def gather_records(local, dist, out=None):
     return out
 
 
+def gather_records_to_root(local, dist, root=0, out=None):
+    """The gateway's collective: every rank's records travel ONCE, to the rank that forwards them (`root`), instead of
+    being replicated on all ranks -- 1/world of the all-gather's bytes over NVLink.  `local`: [n, stride] uint8, same n
+    on every rank.  -> [world * n, stride] rank-major on `root` (written into `out` when given), None elsewhere."""
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    local = local.contiguous()
+    if rank != root:
+        dist.gather(local, gather_list=None, dst=root)
+        return None
+    if out is None:
+        out = torch.empty((world * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    n = local.shape[0]
+    dist.gather(local, gather_list=[out[r * n:(r + 1) * n] for r in range(world)], dst=root)
+    return out
+
+
 def ragged_counts(n_local, dist, device=None):
     """Record counts of every rank (a gateway's ranks own different numbers of packets: channels are balanced by
     samples, not by packets).  One small all-gather at set-up time.  -> list of ints, rank order."""
@@ -49,10 +67,13 @@ def ragged_counts(n_local, dist, device=None):
     return [int(p.item()) for p in parts]
 
 
-def gather_ragged_records(local_padded, dist, out=None):
-    """All-gather of per-packet records when ranks hold different counts: every rank passes a buffer of the SAME
-    padded length (max over `ragged_counts`), rows past its own count are ignored by the reader.  -> [world * n_max,
-    stride]; use `valid_rows` to walk it."""
+def gather_ragged_records(local_padded, dist, out=None, root=None):
+    """Gather of per-packet records when ranks hold different counts: every rank passes a buffer of the SAME padded
+    length (max over `ragged_counts`), rows past its own count are ignored by the reader.  root=None: all-gather
+    (identical on every rank); root=r: only rank r receives (gather_records_to_root).  -> [world * n_max, stride];
+    use `valid_rows` to walk it."""
+    if root is not None:
+        return gather_records_to_root(local_padded, dist, root=root, out=out)
     return gather_records(local_padded, dist, out=out)
 
 

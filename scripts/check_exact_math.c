@@ -37,6 +37,9 @@ int main(int argc, char** argv)
         bad_sin += xm_f2u(s0) != xm_f2u(s1);
         bad_cos += xm_f2u(c0) != xm_f2u(c1);
         bad_sc += (xm_f2u(s2) != xm_f2u(s1)) || (xm_f2u(c2) != xm_f2u(c1));
+        float s3, c3;
+        xm_sincosf_bf(x, &s3, &c3); // the branch-free form the modulator interleaves
+        bad_sc += (xm_f2u(s3) != xm_f2u(s1)) || (xm_f2u(c3) != xm_f2u(c1));
         ++n;
     }
     printf("sinf: %llu mismatches, cosf: %llu mismatches, sincos-internal: %llu of %llu finite floats\n",

@@ -186,3 +186,30 @@ def test_golden_capture_frame_train_is_found(env):
         _, _, info = ORC.chain_decode(env["orc_chain_cfg"](7, 1), want[k].astype(np.uint16))
         assert int(r[k]["hdr_length"]) == info.hdr_length and int(r[k]["hdr_length"]) in (30, 31)
         assert int(r[k]["hdr_has_crc"]) == info.hdr_has_crc and int(r[k]["hdr_rdd"]) == info.hdr_rdd
+
+
+def test_config4_gateway_step_covers_every_packet_once(env):
+    """BASELINE configs[4] at one GPU, reduced to 256 channels: scripts/gateway.py's step (the leg bench.py reports as
+    `extra.gateway`) -- channels of SF7..SF12 assigned by the longest-processing-time rule, demodulated and decoded per
+    SF, records assembled with (channel, sequence) tags.  run() itself asserts that the records cover every (channel,
+    packet) exactly once and that every CRC-valid count is consistent; here also: packets at SNR >= 0 dB decode."""
+    import os
+    import sys
+    import types
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    import gateway
+    line = gateway.run(types.SimpleNamespace(channels=256, sf12_packets=2, steps=1, warmup=3, graph=False), 0, 1, None)
+    assert line["records_cover_every_channel_packet_once"] and line["config"]["channels"] == 256
+    assert line["crc_ok_at_snr_ge_0dB"] > 0.99 and line["value"] > 0
+
+
+def test_config3_stream_leg_of_the_bench(env):
+    """The `extra.stream` leg of bench.py at 64 streams x 2^16 samples: every frame at SNR >= 0 dB found, nothing
+    reported where nothing was sent (bit-level agreement with the oracle is test_config3_mixed_sf_streams_match_oracle)."""
+    import os
+    import sys
+    import types
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    import profile_stream
+    rep = profile_stream.config3(types.SimpleNamespace(streams=64, length=1 << 16, reps=1))
+    assert rep["p_detect_snr_ge_0dB"] >= 0.98 and rep["false_packets"] == 0 and rep["value"] > 0

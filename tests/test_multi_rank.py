@@ -28,7 +28,7 @@ def test_channel_assignment_is_a_balanced_partition():
 def _worker(rank, world, port, q):
     import torch
     import torch.distributed as dist
-    from lora_phy_b200.shard import gather_records, packet_range
+    from lora_phy_b200.shard import gather_records, gather_records_to_root, packet_range
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     n = 64
@@ -42,6 +42,9 @@ def _worker(rank, world, port, q):
     out = gather_records(rec, dist)
     got = out[:, 12:16].contiguous().view(torch.int32).reshape(-1)
     ok = bool(torch.equal(got, torch.arange(world * n, dtype=torch.int32))) and int(out[:, 11].sum()) == world * n
+    # the gateway's form: only the forwarding rank receives
+    at_root = gather_records_to_root(rec, dist, root=0)
+    ok = ok and ((at_root is None) if rank != 0 else bool(torch.equal(at_root, out)))
     # max-over-ranks timing reduction as bench.py does it
     ms = torch.tensor([10.0 + rank], dtype=torch.float64)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
