@@ -156,6 +156,10 @@ struct DemodCfg {
 #ifndef LORA_V_CTAS
 #define LORA_V_CTAS(SF) (LORA_V_PREFETCH ? 2 : ((SF) <= 10 ? 2 : 3))
 #endif
+// Passes whose twiddles stay in registers across the windows a slot walks (bit p = pass p; fft_blocked.cuh PreTw).
+#ifndef LORA_V_PRE
+#define LORA_V_PRE(SF) 0
+#endif
 template <int SF, bool FAITH, bool LIST, bool OSR1>
 __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
 {
@@ -168,6 +172,10 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
     const int slot = threadIdx.x / T;
     const int t = threadIdx.x % T;
     c64* S = smem + slot * B::WIN;
+    constexpr int PREMASK = (!FAITH && !LIST) ? (LORA_V_PRE(SF)) : 0;
+    PreTw pre[PREMASK ? 3 : 1];
+    if (PREMASK & 2) preload_twiddles<SF, 1>(pre[1], t, a.twp);
+    if (PREMASK & 4) preload_twiddles<SF, (B::NP == 3 ? 2 : 1)>(pre[2], t, a.twp);
     const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_packets * a.chunks_per_packet;
     if (LIST && blockIdx.x == 0 && threadIdx.x == 0 && n_items) atomicAdd(a.stat_rechecked, (unsigned long long)n_items);
 
@@ -241,7 +249,7 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
                 const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
                 margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
             }
-            fft_blocked<SF, FAITH>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); });
+            fft_blocked<SF, FAITH, PREMASK>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); }, PREMASK ? pre : nullptr);
             Top best{0.0f, 0, 0.0f};
             bool owner; // the thread that reports this window
             // measured: the winner-reports search is faster for windows of 2 or 4 warps (SF10 +3.6 %, SF11 +5 %) and

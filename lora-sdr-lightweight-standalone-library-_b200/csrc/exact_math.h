@@ -111,6 +111,24 @@ XM_HD uint32_t xm_inv_pio4(int i)
     return w[i];
 }
 
+// The three 32-bit windows the large-argument reduction multiplies by -- entries base, base+4 and base+8 of the table
+// above -- are 96 consecutive bits of ONE bit string (24 zero bits, then the digits of 2/pi) starting 8*base bits in.
+// Cutting them out of four 64-bit words with two funnel shifts costs ~15 instructions; indexing the table with a
+// run-time subscript compiles to a 24-way select chain per entry on the GPU (~70 instructions each).
+XM_HD void xm_inv_pio4_x3(int base, uint32_t* w0, uint32_t* w1, uint32_t* w2)
+{
+    const uint64_t z0 = 0x000000A2F9836E4Eull, z1 = 0x441529FC2757D1F5ull, z2 = 0x34DDC0DB6295993Cull,
+                   z3 = 0x4390410000000000ull;
+    const int up = base >= 8;               // bit offset 8*base is 0..120: word 0 or word 1
+    const uint64_t a = up ? z1 : z0, b = up ? z2 : z1, c = up ? z3 : z2;
+    const int r = (base & 7) * 8;           // 0, 8, ..., 56
+    const uint64_t hi = r ? ((a << r) | (b >> (64 - r))) : a;
+    const uint64_t lo = r ? ((b << r) | (c >> (64 - r))) : b;
+    *w0 = (uint32_t)(hi >> 32);
+    *w1 = (uint32_t)hi;
+    *w2 = (uint32_t)(lo >> 32);
+}
+
 // Evaluate the sine (odd==0) or cosine (odd==1) polynomial.  `neg` flips the cosine's sign (the
 // reference algorithm swaps in a negated coefficient set; negating every coefficient is an exact
 // operation, so flipping the result is bit-identical).
@@ -160,9 +178,11 @@ XM_HD void xm_reduce(float y, double* xr, double* x2, int* quad_odd, int* quad_n
         const int shift = (int)((bits >> 23) & 7u);
         uint32_t xi = (bits & 0xffffffu) | 0x800000u;
         xi <<= shift;
-        uint64_t res0 = (uint64_t)(uint32_t)(xi * xm_inv_pio4(base));
-        const uint64_t res1 = (uint64_t)xi * xm_inv_pio4(base + 4);
-        const uint64_t res2 = (uint64_t)xi * xm_inv_pio4(base + 8);
+        uint32_t w0, w1, w2;
+        xm_inv_pio4_x3(base, &w0, &w1, &w2);
+        uint64_t res0 = (uint64_t)(uint32_t)(xi * w0);
+        const uint64_t res1 = (uint64_t)xi * w1;
+        const uint64_t res2 = (uint64_t)xi * w2;
         res0 = (res2 >> 32) | (res0 << 32);
         res0 += res1;
         const uint64_t nn = (res0 + (1ull << 61)) >> 62;
@@ -226,41 +246,51 @@ XM_HD void xm_sincosf(float y, float* s, float* c)
 }
 
 // Branch-free form of xm_sincosf for code that evaluates several arguments side by side (the chirp modulator
-// interleaves four): both range reductions are computed and one is selected, each polynomial is evaluated exactly
-// once and sine / cosine pick theirs, so there is no divergent path for a scheduler to serialise.  Same bits as
-// xm_sincosf for every float (scripts/check_exact_math.c).  Why the separate |y| < pi/4 path of xm_sincosf is not
-// needed: there the fast reduction yields n = 0 and fma(-0, pi/2, x) = x exactly, i.e. the same polynomial inputs.
-XM_HD void xm_sincosf_bf(float y, float* s, float* c)
+// interleaves four): no divergent path for a scheduler to serialise, each polynomial evaluated exactly once with
+// sine / cosine picking theirs.  `use_small` / `use_large` say which range reductions the caller needs: pass
+// compile-time 1, 1 when nothing is known about y (both are computed, one selected), 1, 0 when the caller knows
+// |y| < 120 (e.g. from a warp vote), 0, 1 when it knows |y| >= 120.  Same bits as xm_sincosf for every float
+// (scripts/check_exact_math.c runs all three forms over all finite floats).  Why the separate |y| < pi/4 path of
+// xm_sincosf is not needed: there the fast reduction yields n = 0 and fma(-0, pi/2, x) = x exactly, i.e. the same
+// polynomial inputs.
+XM_HD void xm_sincosf_paths(float y, float* s, float* c, const int use_small, const int use_large)
 {
     const uint32_t bits = xm_f2u(y);
     const uint32_t top = (bits >> 20) & 0x7ffu;
     const double x = (double)y;
-    // |y| < 120: one multiply and one fused multiply-subtract
-    const double r = XM_DMUL(x, XM_HPI_INV_2P24);
-#if defined(__CUDA_ARCH__)
-    const int32_t ri = __double2int_rz(r); // saturates for arguments the selection below discards
-#else
-    const int32_t ri = (r > -2.0e9 && r < 2.0e9) ? (int32_t)r : 0;
-#endif
-    const int ns = (ri + 0x800000) >> 24;
-    const double xs = XM_DFMA(-(double)ns, XM_HPI, x);
-    // |y| >= 120: 24-bit mantissa times 96 bits of 2/pi
+    double xs = 0.0, xl = 0.0;
+    int ns = 0, nl = 0;
     const int sign = (int)(bits >> 31);
-    const int base = (int)((bits >> 26) & 15u);
-    const int shift = (int)((bits >> 23) & 7u);
-    uint32_t xi = (bits & 0xffffffu) | 0x800000u;
-    xi <<= shift;
-    uint64_t res0 = (uint64_t)(uint32_t)(xi * xm_inv_pio4(base));
-    const uint64_t res1 = (uint64_t)xi * xm_inv_pio4(base + 4);
-    const uint64_t res2 = (uint64_t)xi * xm_inv_pio4(base + 8);
-    res0 = (res2 >> 32) | (res0 << 32);
-    res0 += res1;
-    const uint64_t nn = (res0 + (1ull << 61)) >> 62;
-    res0 -= nn << 62;
-    const double xl = XM_DMUL((double)(int64_t)res0, XM_PI63);
-    const int big = top >= ((0x42f00000u >> 20) & 0x7ffu);
+    if (use_small) { // |y| < 120: one multiply and one fused multiply-subtract
+        const double r = XM_DMUL(x, XM_HPI_INV_2P24);
+#if defined(__CUDA_ARCH__)
+        const int32_t ri = __double2int_rz(r); // saturates for arguments the selection below discards
+#else
+        const int32_t ri = (r > -2.0e9 && r < 2.0e9) ? (int32_t)r : 0;
+#endif
+        ns = (ri + 0x800000) >> 24;
+        xs = XM_DFMA(-(double)ns, XM_HPI, x);
+    }
+    if (use_large) { // |y| >= 120: 24-bit mantissa times 96 bits of 2/pi
+        const int base = (int)((bits >> 26) & 15u);
+        const int shift = (int)((bits >> 23) & 7u);
+        uint32_t xi = (bits & 0xffffffu) | 0x800000u;
+        xi <<= shift;
+        uint32_t w0, w1, w2;
+        xm_inv_pio4_x3(base, &w0, &w1, &w2);
+        uint64_t res0 = (uint64_t)(uint32_t)(xi * w0);
+        const uint64_t res1 = (uint64_t)xi * w1;
+        const uint64_t res2 = (uint64_t)xi * w2;
+        res0 = (res2 >> 32) | (res0 << 32);
+        res0 += res1;
+        const uint64_t nn = (res0 + (1ull << 61)) >> 62;
+        res0 -= nn << 62;
+        xl = XM_DMUL((double)(int64_t)res0, XM_PI63);
+        nl = (int)nn;
+    }
+    const int big = use_large && (!use_small || top >= ((0x42f00000u >> 20) & 0x7ffu));
     const double xx = big ? xl : xs;
-    const int n = big ? (int)nn : ns;
+    const int n = big ? nl : ns;
     const int q = big ? ((n + sign) & 3) : (n & 3);
     const double sgn = (q == 1 || q == 2) ? -1.0 : 1.0;
     const int neg = (q & 2) != 0, odd = n & 1;
@@ -274,6 +304,11 @@ XM_HD void xm_sincosf_bf(float y, float* s, float* c)
     *s = sv;
     *c = cv;
 }
+
+XM_HD void xm_sincosf_bf(float y, float* s, float* c) { xm_sincosf_paths(y, s, c, 1, 1); }
+
+// |y| >= 120 by exponent class (the test glibc's sincosf makes)
+XM_HD int xm_is_large_arg(float y) { return ((xm_f2u(y) >> 20) & 0x7ffu) >= ((0x42f00000u >> 20) & 0x7ffu); }
 
 // ---- atanf / atan2f (fdlibm float algorithm as shipped in glibc 2.39) ------------------------------
 XM_HD float xm_atanf(float x)

@@ -129,10 +129,55 @@ PM_DEV void bfly2(c64& f0, c64& f1, c64 w1, bool trivial, float one)
     f0 = GUARD ? cadd_g<FAITH>(f0, x, one) : add2(f0, x);
 }
 
+// Twiddles of one pass held in registers across windows (fused flavour, small SF): a thread's twiddles depend on its
+// index and the stage only, never on the window, so a slot that walks many windows can load them once.  Per group:
+// entry [0] = the inner stage of the pass (k = klow), entries [1 + c] = the outer stage at k = klow + c * m(b); three
+// multipliers (w^k, w^2k, w^3k) each.  15 complex values for a radix-16 pass, 3 per group for a lone radix-4 stage.
+template <int SF, int P>
+PM_DEV int group_base_klow(int t, int g, int& klow) // klow of group g of thread t in pass P (see group_base below)
+{
+    using B = Blk<SF>;
+    constexpr int mb = B::m(B::pb(P));
+    const int gam = t + B::T * g;
+    klow = P == 0 ? 0 : (gam & (mb - 1));
+    return klow;
+}
+
+struct PreTw {
+    c64 w[4][5][3];
+};
+
+template <int SF, int P>
+PM_DEV void preload_twiddles(PreTw& pre, int t, const c64* __restrict__ tw)
+{
+    using B = Blk<SF>;
+    constexpr int a = B::pa(P), b = B::pb(P), Gp = B::G(P);
+#pragma unroll
+    for (int g = 0; g < Gp; ++g) {
+        int klow;
+        (void)group_base_klow<SF, P>(t, g, klow);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            if (q < B::radix(b) - 1) pre.w[g][0][q] = __ldg(tw + klow + B::toff(b) + q * B::m(b));
+        }
+        if (a != b) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (c < B::radix(b)) {
+#pragma unroll
+                    for (int q = 0; q < 3; ++q)
+                        if (q < B::radix(a) - 1) pre.w[g][1 + c][q] = __ldg(tw + klow + B::toff(a) + c * B::m(b) + q * B::m(a));
+                }
+            }
+        }
+    }
+}
+
 // All stages of pass P on the 16 register-resident points of one thread.  klow[g] = (position mod m_b) of
 // group g (0 in pass 0).  `tw` is the per-stage table (Blk::toff).
-template <int SF, int P, bool FAITH>
-PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restrict__ tw, const Tw0& tw0, float one)
+template <int SF, int P, bool FAITH, bool PRE = false>
+PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restrict__ tw, const Tw0& tw0, float one,
+                        const PreTw* pre = nullptr)
 {
     using B = Blk<SF>;
     constexpr int a = B::pa(P), b = B::pb(P), Rp = B::R(P), Gp = B::G(P), mb = B::m(b);
@@ -159,6 +204,11 @@ PM_DEV void pass_stages(c64 (&v)[16], const int (&klow)[4], const c64* __restric
                         w2 = pk(tw0.w[k * 4 + 2].x, tw0.w[k * 4 + 2].y);
                         w3 = pk(tw0.w[k * 4 + 3].x, tw0.w[k * 4 + 3].y);
                     }
+                } else if (PRE) {
+                    trivial = false;
+                    const int ki = (s == b) ? 0 : 1 + cpart / mb; // compile-time after unrolling
+                    w1 = pre->w[g][ki][0];
+                    if (rs == 4) { w2 = pre->w[g][ki][1]; w3 = pre->w[g][ki][2]; }
                 } else {
                     trivial = false;
                     const c64* wp = tw + klow[g] + (B::toff(s) + cpart); // per-stage table, immediate offsets
@@ -235,9 +285,10 @@ PM_DEV void exchange_load(c64 (&v)[16], int (&klow)[4], const c64* __restrict__ 
 // Whole transform.  `in[j]` = preprocessed input sample t + T*j; on return `v[i]` holds bin bin_of<SF>(t, i).
 // S = this window's shared-memory region (Blk<SF>::WIN entries); sync() = barrier over the window's T threads;
 // tw = the per-stage twiddle table.  The caller must sync() before S is written again (next window).
-template <int SF, bool FAITH, typename Sync>
+// PREMASK: bit p set = pass p takes its twiddles from pre[p] (preload_twiddles) instead of loading them per window.
+template <int SF, bool FAITH, int PREMASK = 0, typename Sync>
 PM_DEV void fft_blocked(const c64 (&in)[16], c64 (&v)[16], c64* __restrict__ S, const c64* __restrict__ tw,
-                        const Tw0& tw0, int t, float one, Sync sync)
+                        const Tw0& tw0, int t, float one, Sync sync, const PreTw* pre = nullptr)
 {
     using B = Blk<SF>;
     int klow[4] = {0, 0, 0, 0};
@@ -247,13 +298,13 @@ PM_DEV void fft_blocked(const c64 (&in)[16], c64 (&v)[16], c64* __restrict__ S, 
     exchange_store<SF, 0>(v, S, t);
     sync();
     exchange_load<SF, 1>(v, klow, S, t);
-    pass_stages<SF, 1, FAITH>(v, klow, tw, tw0, one);
+    pass_stages<SF, 1, FAITH, (PREMASK & 2) != 0>(v, klow, tw, tw0, one, pre ? pre + 1 : nullptr);
     if (B::NP == 3) {
         exchange_store<SF, 1>(v, S, t); // in place: a thread overwrites exactly the positions it read
 
         sync();
         exchange_load<SF, (B::NP == 3 ? 2 : 1)>(v, klow, S, t);
-        pass_stages<SF, (B::NP == 3 ? 2 : 1), FAITH>(v, klow, tw, tw0, one);
+        pass_stages<SF, (B::NP == 3 ? 2 : 1), FAITH, (PREMASK & 4) != 0>(v, klow, tw, tw0, one, pre ? pre + 2 : nullptr);
     }
 }
 

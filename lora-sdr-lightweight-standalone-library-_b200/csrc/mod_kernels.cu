@@ -91,8 +91,21 @@ __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a
             for (int i = 0; i < 4; ++i) y[i] = cur[q + i][lane];
 #pragma unroll
             for (int i = 0; i < 4; ++i) nxt[lane][q + i] = next_phase(); // the recurrence, one chunk ahead
+            // std::polar -> cosf/sinf.  One warp-uniform choice of range reduction for all 128 arguments of this step
+            // (phases inside a chirp are mostly on one side of glibc's |y| < 120 test); never a divergent branch.
+            int large = 0;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) xm_sincosf_bf(y[i], &sn[i], &cs[i]); // std::polar -> cosf/sinf
+            for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
+            if (__all_sync(0xffffffffu, large == 0)) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
+            } else if (__all_sync(0xffffffffu, large == 4)) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
+            }
 #pragma unroll
             for (int i = 0; i < 4; ++i)
                 if (in_range && q + i < warp_live)

@@ -161,9 +161,9 @@ PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red)
 // REDUX gives the warp's largest and the largest among the OTHER lanes; for windows spread over several warps one
 // round through shared memory (two floats per warp) gives every thread the window's maximum.  Only the thread that
 // holds that maximum then looks for the bin index and for the runner-up inside its own 16 values -- a branch that is
-// taken by one thread per window -- and that thread, not thread 0, reports the window.  Returns true in the
-// reporting thread(s).  Exact ties between threads make each of them report with second == max, i.e. untrusted:
-// the bit-faithful recheck then settles the lowest-index rule (a duplicate entry in the recheck list is harmless).
+// taken by one thread per window -- and that thread, not thread 0, reports the window.  Returns true in the one
+// reporting thread.  On an exact tie between threads the elected reporter sets second == max, i.e. untrusted: the
+// bit-faithful recheck then settles the lowest-index rule.
 template <int SF, int TPW>
 PM_DEV bool window_top_fast(const c64 (&v)[16], int t, int slot, float* redw /* 2 * kCta/32 */, Top& out)
 {
@@ -195,7 +195,17 @@ PM_DEV bool window_top_fast(const c64 (&v)[16], int t, int slot, float* redw /* 
 #pragma unroll
         for (int w = 1; w < WARPS; ++w) M = fmaxf(M, wm[w]);
     }
-    const bool winner = top_lane && hi == M && M > 0.0f; // a value that is not > 0 never wins
+    // Exactly ONE thread reports a window: on an exact tie between threads (equal-power bins, structured inputs) the
+    // lowest lane of the lowest warp that holds the maximum is elected, so the recheck list receives at most one entry
+    // per window and can never overflow its n_windows capacity.
+    const bool cand = top_lane && hi == M && M > 0.0f; // a value that is not > 0 never wins
+    const unsigned cands = __ballot_sync(full, cand);
+    int first_holder = 0;
+    if (WARPS > 1) {
+#pragma unroll
+        for (int w = WARPS - 1; w >= 0; --w) if (wm[w] == M) first_holder = w;
+    }
+    const bool winner = cand && (int)(t & 31) == __ffs(cands) - 1 && (WARPS == 1 || (t >> 5) == first_holder);
     if (winner) {
         if (WARPS > 1) {
             const float* rm = redw + slot * 2 * WARPS;

@@ -38,7 +38,10 @@ int main(int argc, char** argv)
         bad_cos += xm_f2u(c0) != xm_f2u(c1);
         bad_sc += (xm_f2u(s2) != xm_f2u(s1)) || (xm_f2u(c2) != xm_f2u(c1));
         float s3, c3;
-        xm_sincosf_bf(x, &s3, &c3); // the branch-free form the modulator interleaves
+        xm_sincosf_bf(x, &s3, &c3); // the branch-free form the modulator interleaves: both reductions, one selected
+        bad_sc += (xm_f2u(s3) != xm_f2u(s1)) || (xm_f2u(c3) != xm_f2u(c1));
+        if (xm_is_large_arg(x)) xm_sincosf_paths(x, &s3, &c3, 0, 1); // ... and with the one reduction a warp vote selects
+        else xm_sincosf_paths(x, &s3, &c3, 1, 0);
         bad_sc += (xm_f2u(s3) != xm_f2u(s1)) || (xm_f2u(c3) != xm_f2u(c1));
         ++n;
     }

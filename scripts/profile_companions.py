@@ -40,9 +40,12 @@ def main():
     ap.add_argument("--sf", type=int, default=12)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--packets", type=int, default=0)
+    ap.add_argument("--lib", default=None, help="variant library (same-box A/B)")
     args = ap.parse_args()
     import torch
     import lora_phy_b200 as L
+    if args.lib:
+        L.LIB_PATH = os.path.abspath(args.lib)
     try:
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
@@ -58,7 +61,7 @@ def main():
         print(f"{name:10s} sf={sf}: {ms:.3f} ms  {gbs:.0f} GB/s = {gbs / peak:.3f} of {peak:.0f} GB/s   {units / ms / 1e3:.1f} {unit}")
 
     if "modulate" in which or "awgn" in which:
-        packets = args.packets or max(4096, (1 << 31) // (35 * n * 8))
+        packets = args.packets or min(65536, (24 << 30) // (35 * n * 8))
         ctx = L.Context(sf)
         g = torch.Generator(device="cuda").manual_seed(1)
         sym = torch.randint(0, n, (packets, 33), dtype=torch.int16, device="cuda", generator=g)
@@ -72,7 +75,7 @@ def main():
             report("awgn", ms, iq.numel() * 16, iq.numel(), "Msamples/s")
         del iq
     if "frame" in which:
-        packets = args.packets or max(4096, (1 << 31) // (50 * n * 8))
+        packets = args.packets or min(65536, (24 << 30) // (50 * n * 8))
         ctx = L.Context(sf)
         g = torch.Generator(device="cuda").manual_seed(2)
         sym = torch.randint(0, n, (packets, 33), dtype=torch.int16, device="cuda", generator=g)

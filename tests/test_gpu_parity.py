@@ -520,3 +520,30 @@ def test_chunked_host_receive_equals_device_path(env):
                 p, r, m = ctx.receive_host_i8(cfg, hn)
             assert bits(p) == bits(want[0]) and bits(r) == bits(want[1]) and bits(m) == bits(want[2]), (name, pinned)
     assert (want[1].view(L.CHAIN_RESULT)["crc_ok"] == 1).mean() > 0.5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sf", [9, 10, 11, 12])
+def test_all_tie_windows_are_rechecked_once_and_resolved_exactly(env, sf):
+    """Every window a lone impulse: a flat spectrum, i.e. (nearly) every bin ties for the maximum.  The fused flavour
+    cannot trust any of them; each window must enter the recheck list exactly once (one elected reporter per window,
+    so the list cannot overflow) and come back with the reference's lowest-index winner."""
+    torch, L, ORC = env["torch"], env["L"], env["ORC"]
+    n = 1 << sf
+    packets, total = 96, 12
+    x = np.zeros((packets, total * n), np.complex64)
+    rng = np.random.default_rng(sf)
+    for p in range(packets):
+        for s in range(total):
+            x[p, s * n + (0 if p % 3 else int(rng.integers(0, n)))] = complex(1.0, 0.0) if p % 2 else complex(0.0, -1.0)
+    ctx = L.Context(sf)
+    ctx.recheck_stats()
+    sym, met, _ = ctx.demod_batch(torch.from_numpy(x).cuda(), mode=L.DEMOD_LEGACY)
+    torch.cuda.synchronize()
+    windows, rechecked = ctx.recheck_stats()
+    assert windows == packets * total and rechecked <= windows
+    assert rechecked >= windows // 2, "flat spectra must not be trusted by the fused flavour"
+    sym = sym.cpu().numpy()
+    for p in range(0, packets, 7):
+        ret, so, sync, mo = ORC.lora_demodulate(sf, x[p])
+        assert bits(sym[p]) == bits(so), (sf, p)
