@@ -10,6 +10,11 @@
  *   - `d_` pointers are device pointers on the context's GPU, `h_` pointers are host pointers.
  *   - Device entry points are stream-ordered on `stream` (a cudaStream_t passed as void*; NULL = the
  *     legacy default stream) and never synchronise or allocate after the first call at a given size.
+ *   - ONE stream in flight per context: a context owns per-call scratch (offset estimates, sync symbols, the recheck
+ *     list, staging buffers), so calls on the same context must be issued on one stream, or ordered by the caller
+ *     (events) when they use several.  Independent work belongs on independent contexts -- they are cheap
+ *     (32-100 KB of tables) and this is how the gateway runs one context per spreading factor.  Host-side entry is
+ *     serialised by a mutex per context; that orders enqueueing, not execution.
  *   - IQ is interleaved little-endian float32 (re, im) = std::complex<float>; symbols are uint16_t.
  *   - There is no CPU fallback anywhere: with no usable CUDA device every call fails with
  *     LORA_B200_ECUDA.
@@ -224,8 +229,8 @@ int lora_b200_compensate_host(lora_b200_ctx* ctx, float cfo, float time_offset, 
  * kissfft<float>::transform (include/lora_phy/kissfft.hh:100-185) and LoRaDetector<float>::detect
  * (include/lora_phy/LoRaDetector.hpp:39-74) for n_windows windows of N = 2^sf samples each, bit for bit the CPU's:
  * the spectrum in natural bin order (inverse != 0: the plan built with inverse = true, kissfft.hh:24-29,176-181), and
- * per window the first-strict-maximum bin of |X|^2, power and powerAvg in dB (minus 20*log10(N)) and the parabolic
- * fIndex.  These are what include/lora_phy/kissfft.hh and LoRaDetector.hpp of this build forward to. */
+ * per window the first-strict-maximum bin of |X|^2, the parabolic fIndex (both bit for bit), and power / powerAvg in
+ * dB minus 20*log10(N) (through the device's log10f: within 3e-5 dB of glibc's; they only feed comparisons).  These are what include/lora_phy/kissfft.hh and LoRaDetector.hpp of this build forward to. */
 typedef struct {
     uint32_t index;      /* LoRaDetector::detect return value */
     float power;         /* :64 */

@@ -1096,8 +1096,14 @@ static int stream_detect_locked(lora_b200_ctx* c, const lora_b200_stream_cfg* cf
         std::vector<float2> all(up);
         all.insert(all.end(), down.begin(), down.end());
         all.insert(all.end(), fine.begin(), fine.end());
-        CU(cudaMalloc(&c->d_stream_tables, sizeof(float2) * all.size()));
-        CU(cudaMemcpy(c->d_stream_tables, all.data(), sizeof(float2) * all.size(), cudaMemcpyHostToDevice));
+        float2* tables = nullptr;
+        CU(cudaMalloc(&tables, sizeof(float2) * all.size()));
+        const cudaError_t up_rc = cudaMemcpy(tables, all.data(), sizeof(float2) * all.size(), cudaMemcpyHostToDevice);
+        if (up_rc != cudaSuccess) { // never leave a non-null, half-written table behind
+            cudaFree(tables);
+            return fail(LORA_B200_ECUDA, "stream table upload", up_rc);
+        }
+        c->d_stream_tables = tables;
     }
     StreamDetectArgs a{};
     a.iq = reinterpret_cast<const float2*>(d_iq);

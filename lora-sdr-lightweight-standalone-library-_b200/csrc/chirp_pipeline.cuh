@@ -1,0 +1,137 @@
+// chirp_pipeline.cuh -- the warp-level engine shared by the two chirp generators (mod_kernels.cu: lora_modulate,
+// stream_kernels.cu: the Pothos frame generator).
+//
+// genChirp (include/lora_phy/ChirpGenerator.hpp:24-50, LoRa-SDR/ChirpGenerator.hpp) is a serial float recurrence over
+// every sample of a packet: f += fStep (wrapped at fMax), phase +-= f, the phase carried from chirp to chirp with one
+// double-precision wrap per chirp (:48).  Float addition is not associative, so only packet-level parallelism
+// reproduces it.  A warp owns 32 packets and walks them in chunks of 32 samples:
+//   * Recurrence: lane l advances packet l, two or three dependent float operations per sample -- a latency chain, not
+//     work.  It runs ONE CHUNK AHEAD, interleaved step by step with the evaluation below (double-buffered in shared
+//     memory), so its latency hides behind the expensive part instead of preceding it.  Chirp bookkeeping (start
+//     frequency, the wrap, the end of the packet) happens once per chunk whenever the chunk lies inside one chirp --
+//     always, for SF >= 7 -- and per sample otherwise.
+//   * Evaluation: phases -> (ampl*cos, ampl*sin) with glibc's cosf/sinf bits (exact_math.h, double-precision
+//     polynomials), lanes across the 32 consecutive samples of one packet so every store is a full 256-byte line.
+//     Four packets are evaluated side by side with the branch-free xm_sincosf_paths: four independent dependency chains
+//     per thread, because with one lane per packet a batch of P packets only ever has P/32 warps to hide latency with
+//     (14 per SM at 65,536 packets), and ONE warp-uniform choice of range reduction per step (phases inside a chirp are
+//     mostly on one side of glibc's |y| < 120 test), never a divergent branch.
+// The caller describes the packet as a list of segments (chirps): segment(s) -> length, start frequency offset, sweep
+// direction.  All packets of a launch share the lengths, so every branch on them is uniform.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "exact_math.h"
+
+namespace lora_b200 {
+
+constexpr int CHIRP_CHUNK = 32;
+
+struct ChirpSegment {
+    int len;    // samples
+    float f0;   // start frequency offset (radians per sample), added to f_min
+    bool down;  // phase -= f instead of += f
+};
+
+struct ChirpSweep {
+    float f_min, f_max, f_step; // ChirpGenerator.hpp:27-29, each evaluated in double and stored as float
+};
+
+// ph: this warp's two chunk buffers, [2][32][CHIRP_CHUNK + 1].  out + q * packet_stride = packet q of the warp.
+template <typename SegFn>
+__device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
+                                               float amplitude, float2* out, size_t packet_stride, int warp_live,
+                                               float (*ph)[32][CHIRP_CHUNK + 1])
+{
+    const int lane = threadIdx.x & 31;
+    const double pi = 3.14159265358979323846;
+    const float span = __fsub_rn(sw.f_max, sw.f_min);
+    float f = 0.0f, phase = 0.0f; // LoRaMod.cpp:13 / LoRa-SDR LoRaMod.cpp:131: the phase starts at zero
+    int s = 0, j = 0, len = 0;
+    bool down = false;
+    auto load_segment = [&]() {
+        if (s < n_segments) {
+            const ChirpSegment g = segment(s);
+            len = g.len;
+            down = g.down;
+            f = __fadd_rn(sw.f_min, g.f0);
+        }
+    };
+    auto step = [&]() -> float { // ChirpGenerator.hpp:33-46
+        f = __fadd_rn(f, sw.f_step);
+        if (f > sw.f_max) f = __fsub_rn(f, span);
+        phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
+        return phase;
+    };
+    auto finish_segment = [&]() { // :48 -- wrap once per chirp, in double, narrowed back into the float accumulator
+        const double pd = (double)phase;
+        phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
+        j = 0;
+        ++s;
+        load_segment();
+    };
+    auto slow_step = [&]() -> float { // a chunk that straddles chirps, or lies past the packet's end
+        if (s >= n_segments) return 0.0f;
+        const float r = step();
+        if (++j == len) finish_segment();
+        return r;
+    };
+    load_segment();
+    while (s < n_segments && len == 0) finish_segment(); // zero-length segments produce nothing
+    bool fast = false;
+    auto begin_chunk = [&]() { fast = s < n_segments && len - j >= CHIRP_CHUNK; };
+    auto end_chunk = [&]() {
+        if (fast) {
+            j += CHIRP_CHUNK;
+            if (j == len) finish_segment();
+        }
+    };
+
+    begin_chunk();
+    for (int i = 0; i < CHIRP_CHUNK; ++i) ph[0][lane][i] = fast ? step() : slow_step();
+    end_chunk();
+    const size_t n_chunks = (n_samples + CHIRP_CHUNK - 1) / CHIRP_CHUNK;
+    for (size_t k = 0; k < n_chunks; ++k) {
+        __syncwarp();
+        const float(*cur)[CHIRP_CHUNK + 1] = ph[k & 1];
+        float(*nxt)[CHIRP_CHUNK + 1] = ph[(k + 1) & 1];
+        const size_t at = k * CHIRP_CHUNK + lane; // this lane's sample in every packet of the warp
+        const bool in_range = at < n_samples;
+        begin_chunk();
+#pragma unroll 1
+        for (int q = 0; q < 32; q += 4) {
+            float y[4], sn[4], cs[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) y[i] = cur[q + i][lane];
+            if (fast) { // the recurrence, one chunk ahead
+#pragma unroll
+                for (int i = 0; i < 4; ++i) nxt[lane][q + i] = step();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) nxt[lane][q + i] = slow_step();
+            }
+            int large = 0; // std::polar -> cosf/sinf
+#pragma unroll
+            for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
+            if (__all_sync(0xffffffffu, large == 0)) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
+            } else if (__all_sync(0xffffffffu, large == 4)) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (in_range && q + i < warp_live)
+                    out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, cs[i]), __fmul_rn(amplitude, sn[i]));
+        }
+        end_chunk();
+    }
+}
+
+} // namespace lora_b200

@@ -131,6 +131,27 @@ PM_DEV void l2_prefetch(const void* p, size_t bytes)
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((unsigned)(hi - lo)) : "memory");
 }
 
+// Sample loads.  LORA_V_NOALLOC = 1: ld.global.nc.L1::no_allocate -- the samples are read once, so they need not
+// push the twiddle and phase tables (re-read by every window) out of L1.  Measured +1.0 / +2.9 / +0.7 % at SF9 / 11 / 12
+// (profiles/r2_ab_kernel_variants.txt); no L2 prefetch at all costs 2-3 %, a two-window prefetch distance changes nothing.
+#ifndef LORA_V_NOALLOC
+#define LORA_V_NOALLOC 1
+#endif
+PM_DEV c64 load_sample(const c64* p)
+{
+#if LORA_V_NOALLOC
+    c64 v;
+    asm("ld.global.nc.L1::no_allocate.b64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+// How many windows ahead the L2 prefetch of a run reaches (0 = none).
+#ifndef LORA_V_PFDIST
+#define LORA_V_PFDIST 1
+#endif
+
 // ---- the hot kernel ---------------------------------------------------------------------------------------------
 // A CTA of 256 threads holds 256/T window slots; each slot walks its own sequence of window chunks (a chunk =
 // `chunk` consecutive windows, normally of one packet, so the per-packet values are loaded once), and slots never
@@ -157,8 +178,14 @@ struct DemodCfg {
 #define LORA_V_CTAS(SF) (LORA_V_PREFETCH ? 2 : ((SF) <= 10 ? 2 : 3))
 #endif
 // Passes whose twiddles stay in registers across the windows a slot walks (bit p = pass p; fft_blocked.cuh PreTw).
+// Measured (profiles/r2_ab_kernel_variants.txt): SF8 +3.7 %, SF9 +1.7 %, SF10 +1.3 %, SF7 +0.8 % -- fewer L1 wavefronts,
+// the unit that binds these sizes.  SF7/8: the 15 twiddles of the radix-16 pass; SF9/10: the 12 of the radix-4 pass.
+// The second exchange of SF11 / SF12 inside a half-warp (fft_blocked.cuh HalfWarp): one barrier fewer per window.
+#ifndef LORA_V_HALFWARP
+#define LORA_V_HALFWARP 0
+#endif
 #ifndef LORA_V_PRE
-#define LORA_V_PRE(SF) 0
+#define LORA_V_PRE(SF) ((SF) <= 8 ? 2 : ((SF) <= 10 ? 4 : 0))
 #endif
 template <int SF, bool FAITH, bool LIST, bool OSR1>
 __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
@@ -173,6 +200,7 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
     const int t = threadIdx.x % T;
     c64* S = smem + slot * B::WIN;
     constexpr int PREMASK = (!FAITH && !LIST) ? (LORA_V_PRE(SF)) : 0;
+    constexpr bool HW = LORA_V_HALFWARP && !FAITH && !LIST && HalfWarp<SF>::OK;
     PreTw pre[PREMASK ? 3 : 1];
     if (PREMASK & 2) preload_twiddles<SF, 1>(pre[1], t, a.twp);
     if (PREMASK & 4) preload_twiddles<SF, (B::NP == 3 ? 2 : 1)>(pre[2], t, a.twp);
@@ -201,10 +229,11 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
             const WinParams q = window_params<SF, FAITH, OSR1>(a, pk_, s);
             const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
             const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
-            if (!LIST && t == 0) { // the samples right after this window: the next window of the run, or of the packet
+            if (!LIST && LORA_V_PFDIST > 0 && t == 0) { // samples after this window: a later window of the run, or of the packet
                 const size_t span = OSR1 ? (size_t)N : (size_t)N * a.osr;
-                const size_t left = a.count - min(a.count, q.base + span);
-                l2_prefetch(x + span, sizeof(c64) * min(span, left));
+                const size_t ahead = span * LORA_V_PFDIST;
+                const size_t left = a.count - min(a.count, q.base + ahead);
+                l2_prefetch(x + ahead, sizeof(c64) * min(span, left));
             }
             c64 in[16], v[16];
             constexpr bool PF = LORA_V_PREFETCH && !FAITH && !LIST && OSR1;
@@ -214,7 +243,7 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
             } else if (OSR1) {
                 const c64* xt = x + t;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) in[j] = __ldg(xt + T * j);
+                for (int j = 0; j < 16; ++j) in[j] = load_sample(xt + T * j);
             } else {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
@@ -249,15 +278,16 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
                 const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
                 margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
             }
-            fft_blocked<SF, FAITH, PREMASK>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); }, PREMASK ? pre : nullptr);
+            fft_blocked<SF, FAITH, PREMASK, HW>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); }, PREMASK ? pre : nullptr);
+            const int tb = HW ? HalfWarp<SF>::u_of(t) : t; // whose bins this thread holds
             Top best{0.0f, 0, 0.0f};
             bool owner; // the thread that reports this window
             // measured: the winner-reports search is faster for windows of 2 or 4 warps (SF10 +3.6 %, SF11 +5 %) and
             // slower for one warp (every warp takes the winner branch) and for eight (SF12 -6 %, longer barrier tail)
             if (!FAITH && (T == 64 || T == 128)) {
-                owner = window_top_fast<SF, (T >= 32 ? T : 32)>(v, t, slot, redw, best);
+                owner = window_top_fast<SF, (T >= 32 ? T : 32)>(v, t, slot, redw, best, tb);
             } else {
-                best = window_top<SF, FAITH, T>(v, t, slot, red);
+                best = window_top<SF, FAITH, T>(v, t, slot, red, tb);
                 owner = t == 0;
             }
             if (owner) {
@@ -514,10 +544,16 @@ template <int SF>
 static void stage_twiddles_sf(const float2* h_tw, std::vector<float2>& out)
 {
     using B = Blk<SF>;
-    out.assign(B::TWP, make_float2(1.0f, 0.0f));
+    out.assign(2 * B::TWP, make_float2(1.0f, 0.0f));
     for (int s = 0; s < B::L; ++s)
         for (int q = 1; q < B::radix(s); ++q)
             for (int k = 0; k < B::m(s); ++k) out[B::toff(s) + (q - 1) * B::m(s) + k] = h_tw[k * B::F(s) * q];
+    // second copy at +TWP: for the half-warp mapping the entries of the last pass (stages 0 and 1, [0, toff(2))) are
+    // reordered inside every block of T so that physical thread t finds the entry of logical thread u_of(t) at +t
+    for (int i = 0; i < B::TWP; ++i) out[B::TWP + i] = out[i];
+    if (HalfWarp<SF>::OK)
+        for (int base = 0; base + B::T <= B::toff(2); base += B::T)
+            for (int t = 0; t < B::T; ++t) out[B::TWP + base + t] = out[base + HalfWarp<SF>::u_of(t)];
 }
 
 std::vector<float2> build_stage_twiddles(int sf, const float2* h_tw)
@@ -553,7 +589,8 @@ static cudaError_t launch_prepass_sf(const PrepassArgs& a, cudaStream_t st)
 {
     constexpr int SLOTS = PreCfg<SF>::SLOTS;
     constexpr size_t smem = sizeof(c64) * PreCfg<SF>::SMEM_C64;
-    static bool attr_done = false;
+    static bool attr_done_dev[kMaxDevices] = {};
+    bool& attr_done = attr_done_dev[current_device_slot()];
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(prepass_blocked_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -571,7 +608,8 @@ static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, cudaStream
     constexpr int SLOTS = DemodCfg<SF>::SLOTS;
     // exchange regions, plus (fast flavour) 16 rotation factors per thread
     constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64;
-    static int per_sm = 0;
+    static int per_sm_dev[kMaxDevices] = {};
+    int& per_sm = per_sm_dev[current_device_slot()];
     if (per_sm == 0) {
         cudaError_t e = cudaFuncSetAttribute(demod_blocked_kernel<SF, FAITH, LIST, OSR1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

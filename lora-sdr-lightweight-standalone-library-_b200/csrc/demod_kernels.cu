@@ -279,7 +279,7 @@ __global__ void fill_est_kernel(float4* est, int n)
     if (p < n) est[p] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
 }
 
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 
 // ---- compensate_offsets (phy.cpp:147-176) ---------------------------------------------------------------------------
 // The reference rotates in place and then moves the samples; out[n] is therefore rotated(in[n - offset]) where that

@@ -5,6 +5,8 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "lora_phy_b200.h"
 
 namespace lora_b200 {
@@ -73,7 +75,17 @@ struct CompensateArgs {
 cudaError_t launch_compensate(const CompensateArgs& a, cudaStream_t st);
 cudaError_t launch_fill_est(float4* est, int n_packets, cudaStream_t st);
 
-extern unsigned long long g_launches; // kernels launched by this library (bench.py's gpu_launches)
+// kernels launched by this library (bench.py's gpu_launches); incremented from whichever host thread launches
+extern std::atomic<unsigned long long> g_launches;
+
+// Function attributes and occupancy are properties of (kernel, device): launchers cache them per device ordinal.
+constexpr int kMaxDevices = 64;
+inline int current_device_slot()
+{
+    int d = 0;
+    cudaGetDevice(&d);
+    return (d >= 0 && d < kMaxDevices) ? d : 0;
+}
 
 // SDR sample ingest: interleaved int16 (I, Q) -> float32 * scale.  With scale = 2^-15 the conversion is exact.
 cudaError_t launch_convert_i16(const short2* in, float2* out, size_t n, float scale, int sm_count, cudaStream_t st);

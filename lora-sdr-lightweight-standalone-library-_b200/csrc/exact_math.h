@@ -115,8 +115,35 @@ XM_HD uint32_t xm_inv_pio4(int i)
 // above -- are 96 consecutive bits of ONE bit string (24 zero bits, then the digits of 2/pi) starting 8*base bits in.
 // Cutting them out of four 64-bit words with two funnel shifts costs ~15 instructions; indexing the table with a
 // run-time subscript compiles to a 24-way select chain per entry on the GPU (~70 instructions each).
+// On the device the sixteen possible triples live in constant memory instead: `base` comes from the argument's
+// exponent, which the lanes of a warp almost always share, so the lookup is three uniform constant loads.
+#if defined(__CUDACC__)
+static __constant__ uint32_t xm_pio4_x3_table[16][4] = {
+    {0x000000a2u, 0xf9836e4eu, 0x441529fcu, 0u},
+    {0x0000a2f9u, 0x836e4e44u, 0x1529fc27u, 0u},
+    {0x00a2f983u, 0x6e4e4415u, 0x29fc2757u, 0u},
+    {0xa2f9836eu, 0x4e441529u, 0xfc2757d1u, 0u},
+    {0xf9836e4eu, 0x441529fcu, 0x2757d1f5u, 0u},
+    {0x836e4e44u, 0x1529fc27u, 0x57d1f534u, 0u},
+    {0x6e4e4415u, 0x29fc2757u, 0xd1f534ddu, 0u},
+    {0x4e441529u, 0xfc2757d1u, 0xf534ddc0u, 0u},
+    {0x441529fcu, 0x2757d1f5u, 0x34ddc0dbu, 0u},
+    {0x1529fc27u, 0x57d1f534u, 0xddc0db62u, 0u},
+    {0x29fc2757u, 0xd1f534ddu, 0xc0db6295u, 0u},
+    {0xfc2757d1u, 0xf534ddc0u, 0xdb629599u, 0u},
+    {0x2757d1f5u, 0x34ddc0dbu, 0x6295993cu, 0u},
+    {0x57d1f534u, 0xddc0db62u, 0x95993c43u, 0u},
+    {0xd1f534ddu, 0xc0db6295u, 0x993c4390u, 0u},
+    {0xf534ddc0u, 0xdb629599u, 0x3c439041u, 0u}};
+#endif
+
 XM_HD void xm_inv_pio4_x3(int base, uint32_t* w0, uint32_t* w1, uint32_t* w2)
 {
+#if defined(__CUDA_ARCH__)
+    *w0 = xm_pio4_x3_table[base][0];
+    *w1 = xm_pio4_x3_table[base][1];
+    *w2 = xm_pio4_x3_table[base][2];
+#else
     const uint64_t z0 = 0x000000A2F9836E4Eull, z1 = 0x441529FC2757D1F5ull, z2 = 0x34DDC0DB6295993Cull,
                    z3 = 0x4390410000000000ull;
     const int up = base >= 8;               // bit offset 8*base is 0..120: word 0 or word 1
@@ -127,6 +154,7 @@ XM_HD void xm_inv_pio4_x3(int base, uint32_t* w0, uint32_t* w1, uint32_t* w2)
     *w0 = (uint32_t)(hi >> 32);
     *w1 = (uint32_t)hi;
     *w2 = (uint32_t)(lo >> 32);
+#endif
 }
 
 // Evaluate the sine (odd==0) or cosine (odd==1) polynomial.  `neg` flips the cosine's sign (the

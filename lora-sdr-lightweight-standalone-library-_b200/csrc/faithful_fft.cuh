@@ -53,13 +53,16 @@ __device__ __forceinline__ int digit_reverse(int i)
 // is a barrier every calling thread reaches.  Threads with active == false do no butterflies (the passes
 // are in place, so a second thread repeating a butterfly would corrupt it) but still take every barrier.  `tw` is the N-entry twiddle table exp(-2*pi*j*i/N) built on the
 // host the way kissfft.hh:24-29 builds it.
-template <int SF, typename Sync>
+// INV = the plan built with inverse = true (kissfft.hh:24-29,176-181): conjugated twiddles (sin(-x) = -sin(x) exactly, so
+// conjugating the forward table gives the inverse table's bits) and the radix-4 rotation by +j instead of -j.
+template <int SF, bool INV = false, typename Sync>
 __device__ __forceinline__ void fft_passes(float2* __restrict__ F, const float2* __restrict__ tw, int t, bool active, Sync sync)
 {
+    auto twd = [&](int i) { float2 w = tw[i]; if (INV) w.y = -w.y; return w; };
     constexpr int N = 1 << SF;
     constexpr int TPW = FftShape<SF>::TPW;
     if (SF & 1) { // innermost radix-2 stage: m = 1, fstride = N/2, twiddle index k*fstride = 0
-        const float2 w0 = tw[0];
+        const float2 w0 = twd(0);
 #pragma unroll
         for (int j = active ? t : N; j < N / 2; j += TPW) {
             const float2 a = F[2 * j], b = F[2 * j + 1];
@@ -77,14 +80,15 @@ __device__ __forceinline__ void fft_passes(float2* __restrict__ F, const float2*
             const int k = j & (m - 1);
             const int base = ((j - k) << 2) + k; // block*4m + k
             const float2 f0 = F[base];
-            const float2 s0 = cmul_rn(F[base + m], tw[k * fstride]);
-            const float2 s1 = cmul_rn(F[base + 2 * m], tw[k * fstride * 2]);
-            const float2 s2 = cmul_rn(F[base + 3 * m], tw[k * fstride * 3]);
+            const float2 s0 = cmul_rn(F[base + m], twd(k * fstride));
+            const float2 s1 = cmul_rn(F[base + 2 * m], twd(k * fstride * 2));
+            const float2 s2 = cmul_rn(F[base + 3 * m], twd(k * fstride * 3));
             const float2 s5 = csub_rn(f0, s1);
             const float2 g0 = cadd_rn(f0, s1);
             const float2 s3 = cadd_rn(s0, s2);
             const float2 d = csub_rn(s0, s2);
-            const float2 s4 = make_float2(d.y, -d.x); // forward transform: (im, -re), kissfft.hh:176-177
+            // forward transform: (im, -re), kissfft.hh:176-177; inverse: (-im, re), :179-180
+            const float2 s4 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);
             F[base + 2 * m] = csub_rn(g0, s3);
             F[base] = cadd_rn(g0, s3);
             F[base + m] = cadd_rn(s5, s4);

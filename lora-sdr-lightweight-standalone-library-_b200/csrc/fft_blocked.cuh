@@ -285,26 +285,48 @@ PM_DEV void exchange_load(c64 (&v)[16], int (&klow)[4], const c64* __restrict__ 
 // Whole transform.  `in[j]` = preprocessed input sample t + T*j; on return `v[i]` holds bin bin_of<SF>(t, i).
 // S = this window's shared-memory region (Blk<SF>::WIN entries); sync() = barrier over the window's T threads;
 // tw = the per-stage twiddle table.  The caller must sync() before S is written again (next window).
+// Half-warp mapping of the last two passes (SF11, SF12: three passes, the last two radix 16).  The sixteen threads that
+// combine at one frequency in the last pass -- those sharing klow of pass 1 -- are made the sixteen lanes of an aligned
+// half-warp by running passes 1 and 2 on the logical index u = (t & 15) * m1 + (t >> 4), m1 = m(pb(1)).  Pass 2 of
+// thread u then reads only what threads of its own half-warp wrote in pass 1, so the SECOND exchange needs
+// __syncwarp() instead of a barrier over the whole window (8 or 4 warps).  Pass 0 keeps the natural index (its global
+// loads must stay coalesced), so the first exchange is unchanged.  Pass-1 twiddles become two addresses per warp
+// (broadcast); pass-2 twiddles would be strided, so they come from a copy of the table permuted by the same map
+// (stored right behind the table, at +TWP: every block of T entries of stages 0 and 1 reordered so that thread t finds
+// the entry of u at offset t).
+template <int SF>
+struct HalfWarp {
+    using B = Blk<SF>;
+    static constexpr bool OK = B::NP == 3 && B::R(1) == 16 && B::R(2) == 16 && B::G(1) == 1 && B::G(2) == 1;
+    static constexpr int M1 = B::m(B::pb(1));
+    __host__ __device__ static constexpr int u_of(int t) { return (t & 15) * M1 + (t >> 4); }
+};
+
 // PREMASK: bit p set = pass p takes its twiddles from pre[p] (preload_twiddles) instead of loading them per window.
-template <int SF, bool FAITH, int PREMASK = 0, typename Sync>
+// HW: the half-warp mapping above (only where HalfWarp<SF>::OK); the caller must use HalfWarp<SF>::u_of(t) for bin_of.
+template <int SF, bool FAITH, int PREMASK = 0, bool HW = false, typename Sync>
 PM_DEV void fft_blocked(const c64 (&in)[16], c64 (&v)[16], c64* __restrict__ S, const c64* __restrict__ tw,
                         const Tw0& tw0, int t, float one, Sync sync, const PreTw* pre = nullptr)
 {
     using B = Blk<SF>;
+    static_assert(!HW || HalfWarp<SF>::OK, "half-warp mapping needs two trailing radix-16 passes");
+    const int u = HW ? HalfWarp<SF>::u_of(t) : t;
     int klow[4] = {0, 0, 0, 0};
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[B::slot0(j)] = in[j];
     pass_stages<SF, 0, FAITH>(v, klow, tw, tw0, one);
     exchange_store<SF, 0>(v, S, t);
     sync();
-    exchange_load<SF, 1>(v, klow, S, t);
+    exchange_load<SF, 1>(v, klow, S, u);
     pass_stages<SF, 1, FAITH, (PREMASK & 2) != 0>(v, klow, tw, tw0, one, pre ? pre + 1 : nullptr);
     if (B::NP == 3) {
-        exchange_store<SF, 1>(v, S, t); // in place: a thread overwrites exactly the positions it read
+        exchange_store<SF, 1>(v, S, u); // in place: a thread overwrites exactly the positions it read
 
-        sync();
-        exchange_load<SF, (B::NP == 3 ? 2 : 1)>(v, klow, S, t);
-        pass_stages<SF, (B::NP == 3 ? 2 : 1), FAITH, (PREMASK & 4) != 0>(v, klow, tw, tw0, one, pre ? pre + 2 : nullptr);
+        if (HW) __syncwarp(); // writers and readers of this exchange share a half-warp
+        else sync();
+        exchange_load<SF, (B::NP == 3 ? 2 : 1)>(v, klow, S, u);
+        if (HW) klow[0] = t; // the permuted table is indexed by the physical thread
+        pass_stages<SF, (B::NP == 3 ? 2 : 1), FAITH, (PREMASK & 4) != 0>(v, klow, HW ? tw + B::TWP : tw, tw0, one, pre ? pre + 2 : nullptr);
     }
 }
 

@@ -10,9 +10,9 @@
 // tests use directly.  One window per CTA on the shared-memory schedule of faithful_fft.cuh (the same butterfly
 // graph as the reference, every operation individually rounded), N/4 threads, all SF 2..12.  Not a throughput path.
 //
-// The inverse transform is conj(FFT(conj(x))): kissfft's inverse plan holds the conjugated twiddles (kissfft.hh:24-29,
-// sin(-x) = -sin(x) exactly) and its radix-4 butterfly rotates by +j instead of -j (:176-181), so every intermediate
-// is the conjugate of the forward graph's on conjugated input -- negation commutes with IEEE rounding, bits included.
+// The inverse transform runs the same graph with the inverse plan's two differences (kissfft.hh:24-29,176-181):
+// conjugated twiddles (sin(-x) = -sin(x) exactly, so the forward table conjugated IS the inverse table) and the radix-4
+// rotation by +j.  (conj(FFT(conj x)) gives the same numbers but the wrong sign on exact zeros.)
 #include "fft_kernels.h"
 
 #include "demod_kernels.h" // g_launches
@@ -36,19 +36,14 @@ __global__ void __launch_bounds__((FftShape<SF>::TPW > 32 ? FftShape<SF>::TPW : 
     for (size_t w = blockIdx.x; w < a.n_windows; w += gridDim.x) {
         const float2* x = a.in + w * (size_t)N;
         for (int i = t; i < N; i += CTA) { // kissfft's leaf copy (kissfft.hh:114-120): digit-reversed scatter
-            float2 v = __ldg(x + i);
-            if (a.inverse) v.y = -v.y;
-            F[digit_reverse<SF>(i)] = v;
+            F[digit_reverse<SF>(i)] = __ldg(x + i);
         }
         __syncthreads();
-        fft_passes<SF>(F, a.tw, t, active, [] { __syncthreads(); });
+        if (a.inverse) fft_passes<SF, true>(F, a.tw, t, active, [] { __syncthreads(); });
+        else fft_passes<SF, false>(F, a.tw, t, active, [] { __syncthreads(); });
         if (a.out) {
             float2* y = a.out + w * (size_t)N;
-            for (int i = t; i < N; i += CTA) {
-                float2 v = F[i];
-                if (a.inverse) v.y = -v.y;
-                y[i] = v;
-            }
+            for (int i = t; i < N; i += CTA) y[i] = F[i];
         }
         if (a.det) { // LoRaDetector.hpp:43-71
             Peak best{0.0f, 0};

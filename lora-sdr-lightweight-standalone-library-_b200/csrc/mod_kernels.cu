@@ -3,36 +3,21 @@
 #include "mod_kernels.h"
 
 #include "demod_kernels.h" // g_launches
+#include "chirp_pipeline.cuh"
 #include "exact_math.h"
 
 namespace lora_b200 {
 
-// genChirp (include/lora_phy/ChirpGenerator.hpp:24-50) is a serial float recurrence over every sample of a
-// packet: f += fStep (wrapped at fMax), phase += f, and the phase is carried from symbol to symbol
-// (LoRaMod.cpp:13,25-41) with one double-precision wrap per symbol (:48).  Float addition is not
-// associative, so only packet-level parallelism reproduces it.  Layout: a warp owns 32 packets and walks them in
-// chunks of 32 samples.
-//   * Recurrence: lane l advances packet l, two dependent float adds per sample -- a latency chain, not work.  It
-//     runs ONE CHUNK AHEAD, interleaved step by step with the evaluation below (double-buffered in shared memory),
-//     so its latency is hidden behind the expensive part instead of preceding it.
-//   * Evaluation: phases -> (ampl*cos, ampl*sin) with glibc's cosf/sinf bits (exact_math.h, double-precision
-//     polynomials), lanes across the 32 consecutive samples of one packet so every store is a full 256-byte line.
-//     Four packets are evaluated side by side with the branch-free xm_sincosf_bf: four independent dependency
-//     chains per thread, because with one lane per packet a batch of P packets only ever has P/32 warps to hide
-//     latency with (14 per SM at 65,536 packets).
-// Algorithmic bytes: 8*N*osr written per symbol (+2 read); bound: issue slots of the fp64-exact sincos (~70
-// instructions per sample), about 0.6 of the HBM write roofline.
-constexpr int MOD_CHUNK = 32;
+// lora_modulate (src/phy/LoRaMod.cpp:8-43): two sync chirps and one up-chirp per symbol, every one a genChirp call
+// that shares one float phase.  The recurrence / evaluation engine is chirp_pipeline.cuh; this kernel only describes the
+// packet: segment s = sync word 0, sync word 1, then the data symbols, each N*osr samples.
+// Algorithmic bytes: 8*N*osr written per symbol (+2 read); bound: issue slots of the fp64-exact sincos (~90
+// instructions per sample), i.e. about a third of the HBM write roofline.
 constexpr int MOD_WARPS = 4;
-
-struct ChirpState { // one packet's genChirp / lora_modulate state, held by one lane
-    float f, phase;
-    int s, j;       // symbol index (sync words first) and sample index inside it
-};
 
 __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a)
 {
-    __shared__ float ph[MOD_WARPS][2][32][MOD_CHUNK + 1];
+    __shared__ float ph[MOD_WARPS][2][32][CHIRP_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pk0 = (blockIdx.x * MOD_WARPS + warp) * 32;
     if (pk0 >= a.n_packets) return; // whole warp
@@ -41,78 +26,21 @@ __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a
     const int N = 1 << a.sf;
     const int step = N * a.osr;
     const double pi = 3.14159265358979323846;
-    // :27-29 -- evaluated in double, stored as float
-    const float f_min = (float)__ddiv_rn(__dmul_rn(-pi, (double)a.bw_scale), (double)a.osr);
-    const float f_max = (float)__ddiv_rn(__dmul_rn(pi, (double)a.bw_scale), (double)a.osr);
-    const float f_step = (float)__ddiv_rn(__dmul_rn(2 * pi, (double)a.bw_scale), (double)(N * a.osr * a.osr));
-    const float span = __fsub_rn(f_max, f_min);
+    ChirpSweep sw; // ChirpGenerator.hpp:27-29 -- evaluated in double, stored as float
+    sw.f_min = (float)__ddiv_rn(__dmul_rn(-pi, (double)a.bw_scale), (double)a.osr);
+    sw.f_max = (float)__ddiv_rn(__dmul_rn(pi, (double)a.bw_scale), (double)a.osr);
+    sw.f_step = (float)__ddiv_rn(__dmul_rn(2 * pi, (double)a.bw_scale), (double)(N * a.osr * a.osr));
     const float pi_f = 3.14159274101257324f;
     const float denom = __fmul_rn((float)N, (float)a.osr);
     const uint16_t* sym = a.symbols + (size_t)(live ? pk : pk0) * a.symbol_stride;
     const int total = (int)a.n_symbols + 2;
-    const int warp_live = min(32, a.n_packets - pk0);
-    const size_t n_samples = (size_t)total * step;
-    const size_t n_chunks = (n_samples + MOD_CHUNK - 1) / MOD_CHUNK;
-
-    ChirpState st{0.0f, 0.0f, 0, 0}; // LoRaMod.cpp:13: phase = 0
-    // One step of the recurrence: the phase of the next sample of this lane's packet (any value past the packet's end).
-    auto next_phase = [&]() -> float {
-        if (st.s >= total) return 0.0f;
-        if (st.j == 0) {
-            const unsigned v = st.s == 0 ? a.sw0 : st.s == 1 ? a.sw1 : (unsigned)sym[st.s - 2];
-            // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
-            const float f0 = __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom);
-            st.f = __fadd_rn(f_min, f0);
-        }
-        st.f = __fadd_rn(st.f, f_step);                 // ChirpGenerator.hpp:41-45 (up-chirp branch)
-        if (st.f > f_max) st.f = __fsub_rn(st.f, span);
-        st.phase = __fadd_rn(st.phase, st.f);
-        const float out = st.phase;
-        if (++st.j == step) { // :48 -- wrap once per chirp, in double, narrowed back into the float accumulator
-            const double pd = (double)st.phase;
-            st.phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
-            st.j = 0;
-            ++st.s;
-        }
-        return out;
+    auto segment = [&](int s) {
+        const unsigned v = s == 0 ? a.sw0 : s == 1 ? a.sw1 : (unsigned)sym[s - 2];
+        // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
+        return ChirpSegment{step, __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom), false};
     };
-
-    for (int j = 0; j < MOD_CHUNK; ++j) ph[warp][0][lane][j] = next_phase();
-    for (size_t k = 0; k < n_chunks; ++k) {
-        __syncwarp();
-        const float(*cur)[MOD_CHUNK + 1] = ph[warp][k & 1];
-        float(*nxt)[MOD_CHUNK + 1] = ph[warp][(k + 1) & 1];
-        const size_t at = k * MOD_CHUNK + lane;           // this lane's sample in every packet of the warp
-        const bool in_range = at < n_samples;
-#pragma unroll 1
-        for (int q = 0; q < 32; q += 4) {
-            float y[4], sn[4], cs[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) y[i] = cur[q + i][lane];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) nxt[lane][q + i] = next_phase(); // the recurrence, one chunk ahead
-            // std::polar -> cosf/sinf.  One warp-uniform choice of range reduction for all 128 arguments of this step
-            // (phases inside a chirp are mostly on one side of glibc's |y| < 120 test); never a divergent branch.
-            int large = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
-            if (__all_sync(0xffffffffu, large == 0)) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
-            } else if (__all_sync(0xffffffffu, large == 4)) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (in_range && q + i < warp_live)
-                    a.iq[(size_t)(pk0 + q + i) * a.packet_stride + at] =
-                        make_float2(__fmul_rn(a.amplitude, cs[i]), __fmul_rn(a.amplitude, sn[i]));
-        }
-    }
+    chirp_pipeline(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
+                   a.packet_stride, min(32, a.n_packets - pk0), ph[warp]);
 }
 
 // ---- AWGN --------------------------------------------------------------------------------------------------

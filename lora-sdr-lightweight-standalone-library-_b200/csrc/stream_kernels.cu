@@ -13,6 +13,7 @@
 #include <cmath>
 
 #include "demod_kernels.h" // g_launches
+#include "chirp_pipeline.cuh"
 #include "exact_math.h"
 #include "window_common.cuh"
 
@@ -372,14 +373,15 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
 }
 
 // ---- frame generator --------------------------------------------------------------------------------------------
-// Same layout as mod_kernels.cu: genChirp (LoRa-SDR/ChirpGenerator.hpp) is a serial float recurrence with the phase
-// carried through the whole frame, so a lane owns a frame for the recurrence and the warp shares the cos/sin work.
-constexpr int FM_CHUNK = 32;
+// Same engine as mod_kernels.cu (chirp_pipeline.cuh): genChirp (LoRa-SDR/ChirpGenerator.hpp) is a serial float recurrence
+// with the phase carried through the whole frame, so a lane owns a frame for the recurrence and the warp shares the
+// cos/sin work.  This kernel describes the frame of LoRaMod.cpp:138-208: 10 up-chirps, 2 sync chirps, 2 down-chirps, a
+// quarter down-chirp, the data symbols; then the zero padding of :217-228.
 constexpr int FM_WARPS = 4;
 
 __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModArgs a)
 {
-    __shared__ float ph[FM_WARPS][32][FM_CHUNK + 1];
+    __shared__ float ph[FM_WARPS][2][32][CHIRP_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pk0 = (blockIdx.x * FM_WARPS + warp) * 32;
     if (pk0 >= a.n_packets) return; // whole warp
@@ -388,53 +390,28 @@ __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModA
     const int N = 1 << a.sf;
     const int NN = N * a.osr;
     const double pi = 3.14159265358979323846;
-    const float f_min = (float)__ddiv_rn(-pi, (double)a.osr);
-    const float f_max = (float)__ddiv_rn(pi, (double)a.osr);
-    const float f_step = (float)__ddiv_rn(2 * pi, (double)(N * a.osr * a.osr));
-    const float span = __fsub_rn(f_max, f_min);
+    ChirpSweep sw;
+    sw.f_min = (float)__ddiv_rn(-pi, (double)a.osr);
+    sw.f_max = (float)__ddiv_rn(pi, (double)a.osr);
+    sw.f_step = (float)__ddiv_rn(2 * pi, (double)(N * a.osr * a.osr));
     const uint16_t* sym = a.symbols + (size_t)(live ? pk : pk0) * a.symbol_stride;
     const int segments = 15 + (int)a.n_symbols; // 10 up, 2 sync, 2 down, 1/4 down, data (LoRaMod.cpp:138-208)
     const int warp_live = min(32, a.n_packets - pk0);
-
-    float phase = 0.0f; // :131
-    size_t at = 0;
-    for (int s = 0; s < segments; ++s) {
-        const bool down = s >= 12 && s < 15;
-        const int len = s == 14 ? NN / 4 : NN;
+    auto segment = [&](int s) {
         int v = 0;
         if (s == 10) v = (int)(a.sync >> 4) * 8;          // :150
         else if (s == 11) v = (int)(a.sync & 0xfu) * 8;   // :162
         else if (s >= 15) v = sym[s - 15];                // :205
         // freq = (2*M_PI*sym)/NN in double, narrowed to the float argument of genChirp
-        const float f0 = (float)__ddiv_rn(__dmul_rn(2 * pi, (double)v), (double)NN);
-        float f = __fadd_rn(f_min, f0);
-        for (int c0 = 0; c0 < len; c0 += FM_CHUNK) {
-            const int n = min(FM_CHUNK, len - c0);
-            for (int j = 0; j < n; ++j) {
-                f = __fadd_rn(f, f_step);
-                if (f > f_max) f = __fsub_rn(f, span);
-                phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
-                ph[warp][lane][j] = phase;
-            }
-            __syncwarp();
-            for (int q = 0; q < warp_live; ++q) {
-                if (lane < n) {
-                    float sn, cs;
-                    xm_sincosf(ph[warp][q][lane], &sn, &cs);
-                    a.iq[(size_t)(pk0 + q) * a.packet_stride + at + c0 + lane] =
-                        make_float2(__fmul_rn(a.amplitude, cs), __fmul_rn(a.amplitude, sn));
-                }
-            }
-            __syncwarp();
-        }
-        at += (size_t)len;
-        const double pd = (double)phase; // one wrap per chirp, in double
-        phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
-    }
+        return ChirpSegment{s == 14 ? NN / 4 : NN, (float)__ddiv_rn(__dmul_rn(2 * pi, (double)v), (double)NN), s >= 12 && s < 15};
+    };
+    const size_t n_samples = (size_t)(14 + a.n_symbols) * NN + NN / 4;
+    float2* out = a.iq + (size_t)pk0 * a.packet_stride;
+    chirp_pipeline(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
     // :224-226 zero padding
     const size_t pad = (size_t)(a.padding ? a.padding : 1u) * NN; // the counter is incremented before the test (:219-221)
     for (int q = 0; q < warp_live; ++q)
-        for (size_t i = lane; i < pad; i += 32) a.iq[(size_t)(pk0 + q) * a.packet_stride + at + i] = make_float2(0.0f, 0.0f);
+        for (size_t i = lane; i < pad; i += 32) out[(size_t)q * a.packet_stride + n_samples + i] = make_float2(0.0f, 0.0f);
 }
 
 template <int SF>
@@ -442,7 +419,8 @@ cudaError_t launch_stream_sf(const StreamDetectArgs& a, int sm_count, cudaStream
 {
     constexpr int SLOTS = StreamCfg<SF>::SLOTS;
     const size_t smem = sizeof(c64) * StreamCfg<SF>::SMEM_C64;
-    static bool configured = false;
+    static bool configured_dev[kMaxDevices] = {};
+    bool& configured = configured_dev[current_device_slot()];
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(stream_detect_kernel<SF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

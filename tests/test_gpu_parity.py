@@ -482,8 +482,13 @@ def test_overlapped_scan_equals_two_pass_path(env, sf, mode_name):
     a, b = out[0][2], out[1][2]
     assert ((a == b) | (np.isnan(a) & np.isnan(b))).all(), "peaks differ"
     met = out[1][1].view(L.PKT_METRICS).reshape(-1)
-    assert met["max_amp"][1] == 0 and np.isinf(met["max_amp"][4]) and met["max_amp"][5] == 77.0 and met["max_amp"][3] >= 40.0
-    assert met["normalised"][6] == 0 and met["normalised"][0] == 1
+    # The equality above is the test.  The spot checks below pin what the planted samples mean in legacy mode, where
+    # the scan sees the samples themselves; in fused-dechirp mode it sees iq * down[n], where a NaN in either component
+    # poisons both, so the planted (40, NaN) never counts and the maxima are whatever the noise left.
+    assert met["max_amp"][1] == 0 and np.isinf(met["max_amp"][4])
+    if mode_name == "legacy":
+        assert met["max_amp"][5] == 77.0 and met["max_amp"][3] >= 40.0
+        assert met["normalised"][6] == 0 and met["normalised"][0] == 1
 
 
 @pytest.mark.gpu
