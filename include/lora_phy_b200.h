@@ -244,7 +244,8 @@ int lora_b200_fft_detect_host(lora_b200_ctx* ctx, const lora_b200_c32* h_in, siz
                               lora_b200_c32* h_spectrum /* nullable */, lora_b200_detect_result* h_results /* nullable */);
 
 /* Batched host-buffer demod + chain decode: the end-to-end call bench.py times (pinned or pageable host
- * memory in, payloads and results out). */
+ * memory in, payloads and results out).  Payload bytes the decoder does not write (dropped packets, bytes past
+ * n_bytes) come back as zero. */
 int lora_b200_receive_host(lora_b200_ctx* ctx, int mode, const lora_b200_chain_cfg* cfg,
                            const lora_b200_c32* h_iq, size_t n_packets, size_t samples_per_packet,
                            uint8_t* h_payload, lora_b200_chain_result* h_results,

@@ -877,6 +877,8 @@ static int receive_host_chunked(lora_b200_ctx* c, int mode, const lora_b200_chai
         lora_b200_chain_result* d_res = c->s_results.as<lora_b200_chain_result>() + p0;
         int rc = demod_batch_locked(c, mode, d_iq, pn, count, count, d_sym, nsym, nullptr, d_met, st);
         if (rc) return rc;
+        // a dropped packet writes no payload bytes: the caller gets zeros there, not whatever the staging buffer held
+        CU(cudaMemsetAsync(d_pay, 0, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * pn, st));
         rc = chain_decode_locked(c, g, d_sym, pn, nsym, nsym, d_pay, d_res, st);
         if (rc) return rc;
         CU(cudaMemcpyAsync(h_payload + p0 * LORA_B200_PAYLOAD_STRIDE, d_pay, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * pn,
@@ -1199,6 +1201,7 @@ extern "C" int lora_b200_std_receive_stream_host(lora_b200_ctx* c, const lora_b2
     if (int rc = stream_detect_locked(c, &sc, c->s_iq.as<lora_b200_c32>(), 1, count, count, c->s_sym.as<int16_t>(), d_pk,
                                       d_res, st))
         return rc;
+    CU(cudaMemsetAsync(c->s_payload.p, 0, static_cast<size_t>(LORA_B200_PAYLOAD_STRIDE) * np, st)); // bytes no frame writes read as zero
     CU(launch_std_decode(a, st));
     lora_b200_stream_result res{};
     CU(cudaMemcpyAsync(&res, d_res, sizeof(res), cudaMemcpyDeviceToHost, st));
