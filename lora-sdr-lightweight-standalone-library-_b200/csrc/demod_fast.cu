@@ -181,8 +181,9 @@ struct DemodCfg {
 // Measured (profiles/r2_ab_kernel_variants.txt): SF8 +3.7 %, SF9 +1.7 %, SF10 +1.3 %, SF7 +0.8 % -- fewer L1 wavefronts,
 // the unit that binds these sizes.  SF7/8: the 15 twiddles of the radix-16 pass; SF9/10: the 12 of the radix-4 pass.
 // The second exchange of SF11 / SF12 inside a half-warp (fft_blocked.cuh HalfWarp): one barrier fewer per window.
+// Measured on two boxes: SF11 +0.8 / +1.1 %, SF12 +1.3 / +1.3 % (profiles/r2_ab_kernel_variants.txt).
 #ifndef LORA_V_HALFWARP
-#define LORA_V_HALFWARP 0
+#define LORA_V_HALFWARP 1
 #endif
 #ifndef LORA_V_PRE
 #define LORA_V_PRE(SF) ((SF) <= 8 ? 2 : ((SF) <= 10 ? 4 : 0))

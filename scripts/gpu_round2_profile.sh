@@ -1,16 +1,13 @@
-# Round-2 evidence run (one gpurun call): same-box A/Bs, then the ncu captures DESIGN.md / profiles/README.md cite.
+# Round-2 evidence run (one gpurun call): bench lines, then the ncu captures DESIGN.md / profiles/README.md cite.
 # Every ncu command runs only after the same command line has exited 0 without ncu in this call.  The .ncu-rep files
 # are summarised ON the box (scripts/ncu_summary.py, the SASS page gzipped) and deleted: gpurun_out/ is capped at 64 MiB.
 set -x
 cd "$(dirname "$0")/.."
 O=gpurun_out
-python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-# --- A/B: modulator old vs new at 65,536 packets; demod-kernel variants at SF11/12
-for sf in 7 10 12; do
-  python scripts/profile_companions.py --sf $sf --which modulate --packets 65536 2>&1 | grep "^modulate" | sed 's/^/new /'
-  python scripts/profile_companions.py --sf $sf --which modulate --packets 65536 --lib ab/modold/liblora_phy_b200.so 2>&1 | grep -E "^modulate|Error|error" | tail -2 | sed 's/^/old /'
-done 2>/dev/null | tee $O/r2_ab_modulator.txt
-SFS="9 11 12" scripts/ab_run.sh noalloc pf0 pf2 napf2 2>/dev/null | tee $O/r2_ab4.txt
+mkdir -p $O
+# --- the bench lines (never under ncu)
+python bench.py > $O/r2_bench_1gpu.json 2> $O/r2_bench_1gpu.err; echo bench rc=$?
+python bench.py --impl reference --steps 2 --warmup 1 > $O/r2_bench_reference_arm.json 2> $O/r2_bench_reference_arm.err; echo ref rc=$?
 # --- launch list of the bench command
 python bench.py --steps 2 --warmup 1 --no-extras --no-perf-test > $O/bench_short.json 2> $O/bench_short.err && \
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/r2_ncu_launches_bench.csv \
@@ -36,4 +33,4 @@ python scripts/profile_companions.py --which stream7 > $O/ps7.log 2>&1 && \
 digest prof_s7 r2_ncu_stream7
 rm -f $O/*.ncu-rep
 du -sh $O; ls -la $O | tail -30
-cat $O/r2_ab_modulator.txt $O/r2_ab4.txt
+head -c 1500 $O/r2_bench_1gpu.json; echo; head -c 600 $O/r2_bench_reference_arm.json
