@@ -166,6 +166,25 @@ int lora_b200_demod_batch(lora_b200_ctx* ctx, int mode, const lora_b200_c32* d_i
                           size_t symbol_stride, float* d_peaks, lora_b200_pkt_metrics* d_metrics,
                           void* stream);
 
+/* lora_b200_demod_batch for callers that cannot allocate (code under CUDA stream capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same results bit for bit, SF7..SF12 only.  The per-call scratch of the receive kernels (offset
+ * estimates, raw sync symbols, the recheck list) lives in a fixed device array inside the library -- about 4.3 MB that
+ * every GPU which loads the library holds until the process exits -- so the call issues no cudaMalloc / cudaFree and
+ * no host allocation; it only enqueues kernels and one 4-byte memset on `stream`.  Limits, checked with
+ * LORA_B200_EINVAL and a message in lora_b200_last_error(): at most LORA_B200_STATIC_MAX_PACKETS packets and
+ * LORA_B200_STATIC_MAX_WINDOWS symbol windows (n_packets * (samples_per_packet / (N*osr))) per call.
+ * All calls on one device share the array: calls that overlap on the GPU (different streams, contexts or host
+ * threads) race on it -- order them on one stream or with events.  It keeps the last call's contents; the word that
+ * must start at zero is cleared on `stream` by the call itself.  Kernel timing (lora_b200_set_kernel_timing) and the
+ * overlapped scan (lora_b200_set_overlap) do not apply to this entry point. */
+#define LORA_B200_STATIC_MAX_PACKETS 16384
+#define LORA_B200_STATIC_MAX_WINDOWS 1048576
+int lora_b200_demod_batch_static(lora_b200_ctx* ctx, int mode, const lora_b200_c32* d_iq, size_t n_packets,
+                                 size_t samples_per_packet, size_t packet_stride, uint16_t* d_symbols,
+                                 size_t symbol_stride, float* d_peaks, lora_b200_pkt_metrics* d_metrics,
+                                 void* stream);
+
 /* lora_phy::estimate_offsets (phy.cpp:78-145) over a batch; writes cfo/time_offset of d_metrics. */
 int lora_b200_estimate_batch(lora_b200_ctx* ctx, const lora_b200_c32* d_iq, size_t n_packets,
                              size_t samples_per_packet, size_t packet_stride,

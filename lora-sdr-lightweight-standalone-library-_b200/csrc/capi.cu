@@ -479,6 +479,135 @@ extern "C" int lora_b200_demod_batch(lora_b200_ctx* c, int mode, const lora_b200
                               static_cast<cudaStream_t>(stream));
 }
 
+// ---- receive path without allocation ----------------------------------------------------------------------
+// lora_b200_demod_batch_static: the blocked receive kernels (prepass -> fused demod -> recheck -> finalize) with their
+// per-call scratch -- offset estimates, raw sync symbols, the recheck list -- in a fixed file-scope device array
+// instead of the context's grow-only buffers.  Nothing is allocated or freed, on the device or on the host, so the
+// call is usable where cudaMalloc is not (stream capture, serving loops).  Every GPU that loads this library holds
+// the array (kStaticScratchBytes, about 4.3 MB) until the process exits.  All calls on a device SHARE it and it keeps
+// the previous call's contents: the one word that must start at zero (the recheck count) is cleared on the stream by
+// the launcher (cudaMemsetAsync), everything else is written before it is read.  Calls that overlap on the GPU --
+// two streams, two contexts, two host threads -- race on it; the caller orders them.
+constexpr size_t kStaticMaxPackets = LORA_B200_STATIC_MAX_PACKETS;
+constexpr size_t kStaticMaxWindows = LORA_B200_STATIC_MAX_WINDOWS;
+constexpr size_t kStaticEstOff = 0;                                                        // float4[packets]
+constexpr size_t kStaticSyncOff = kStaticEstOff + sizeof(float4) * kStaticMaxPackets;     // uint16_t[2 * packets]
+constexpr size_t kStaticFlagOff = kStaticSyncOff + sizeof(uint16_t) * 2 * kStaticMaxPackets; // unsigned[1 + windows]
+constexpr size_t kStaticScratchBytes = ((kStaticFlagOff + sizeof(unsigned) * (kStaticMaxWindows + 1)) + 255) / 256 * 256;
+static_assert(kStaticSyncOff % 256 == 0 && kStaticFlagOff % 256 == 0, "sections stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address is looked up
+// once per device, with that device current, and cached.  (The lookup does not allocate; the array came with the module.)
+static int static_scratch_base(int device, unsigned char** out)
+{
+    static std::mutex mu;
+    static unsigned char* base[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) return fail(LORA_B200_EINVAL, "device ordinal beyond the static scratch table");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!base[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) return fail(LORA_B200_ECUDA, "cudaGetSymbolAddress(static scratch)", e);
+        base[device] = static_cast<unsigned char*>(p);
+    }
+    *out = base[device];
+    return LORA_B200_OK;
+}
+
+extern "C" int lora_b200_demod_batch_static(lora_b200_ctx* c, int mode, const lora_b200_c32* d_iq_, size_t n_packets,
+                                            size_t count, size_t packet_stride, uint16_t* d_symbols,
+                                            size_t symbol_stride, float* d_peaks, lora_b200_pkt_metrics* d_metrics,
+                                            void* stream)
+{
+    if (!c) return fail(LORA_B200_EINVAL, "null context");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const float2* d_iq = reinterpret_cast<const float2*>(d_iq_);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int sf = static_cast<int>(c->cfg.sf);
+    const size_t N = static_cast<size_t>(c->n), osr = c->cfg.osr, step = N * osr;
+    const bool legacy = mode != LORA_B200_DEMOD_WORKSPACE;
+    if (mode < 0 || mode > 2) return fail(LORA_B200_EINVAL, "unknown demod mode");
+    if (!blocked_supported(sf)) return fail(LORA_B200_EINVAL, "lora_b200_demod_batch_static needs sf 7..12");
+    if (!d_iq || !d_symbols) return fail(LORA_B200_EINVAL, "null buffer");
+    if (n_packets == 0) return LORA_B200_OK;
+    if (n_packets > kStaticMaxPackets)
+        return fail(LORA_B200_EINVAL, "lora_b200_demod_batch_static: more than LORA_B200_STATIC_MAX_PACKETS (16384) packets");
+    if (packet_stride < count) return fail(LORA_B200_EINVAL, "packet_stride < samples_per_packet");
+    const size_t total = count / step;
+    if (!legacy) {
+        if (count % step != 0) return fail(LORA_B200_EINVAL, "sample count not a multiple of N*osr");
+        if (total < 2) return fail(LORA_B200_EINVAL, "fewer than two symbols");
+    }
+    if (mode == LORA_B200_DEMOD_LEGACY_DECHIRP && (osr != 1 || count % N != 0))
+        return fail(LORA_B200_EINVAL, "fused caller-dechirp needs osr == 1 and whole symbols");
+    const bool have_sync = total >= 2;
+    const size_t n_out = have_sync ? total - 2 : total;
+    if (symbol_stride < n_out) return fail(LORA_B200_EINVAL, "symbol_stride too small");
+    if (total > 0xffff) return fail(LORA_B200_EINVAL, "more than 65535 symbols per packet");
+    if (n_packets * total > kStaticMaxWindows)
+        return fail(LORA_B200_EINVAL,
+                    "lora_b200_demod_batch_static: more than LORA_B200_STATIC_MAX_WINDOWS (1048576) symbol windows in one call");
+
+    unsigned char* base = nullptr;
+    if (int rc = static_scratch_base(c->device, &base)) return rc;
+    float4* est = reinterpret_cast<float4*>(base + kStaticEstOff);
+    uint16_t* sync_raw = reinterpret_cast<uint16_t*>(base + kStaticSyncOff);
+    unsigned* flags = reinterpret_cast<unsigned*>(base + kStaticFlagOff);
+    const int np = static_cast<int>(n_packets);
+    const bool dechirp_in = mode == LORA_B200_DEMOD_LEGACY_DECHIRP;
+
+    PrepassArgs pa{};
+    pa.iq = d_iq; pa.packet_stride = packet_stride; pa.count = count;
+    pa.n_packets = np;
+    pa.do_maxabs = legacy && count > 0;
+    pa.symbols = static_cast<int>(total < 2 ? total : 2);
+    pa.osr = static_cast<int>(osr);
+    pa.dechirp = dechirp_in;
+    pa.use_scale = legacy;
+    pa.legacy_tie = legacy;
+    pa.twp = reinterpret_cast<const c64*>(c->d_twp); pa.down = reinterpret_cast<const c64*>(c->d_down);
+    pa.window = c->d_window;
+    pa.power_scale = c->power_scale;
+    pa.est = est;
+    pa.tw0 = c->tw0; pa.one = 1.0f;
+    CU(launch_prepass_blocked(sf, pa, st));
+    if (total > 0) {
+        BlockedDemodArgs da{};
+        da.iq = d_iq; da.packet_stride = packet_stride; da.count = count;
+        da.n_windows = static_cast<unsigned>(n_packets * total);
+        da.n_packets = static_cast<unsigned>(n_packets);
+        da.total = static_cast<int>(total);
+        da.div_total = make_fastdiv(static_cast<unsigned>(total));
+        da.osr = static_cast<int>(osr);
+        da.dechirp = mode != LORA_B200_DEMOD_LEGACY;
+        da.dechirp_absolute = dechirp_in;
+        da.use_scale = legacy;
+        da.have_sync = have_sync;
+        da.twp = pa.twp; da.down = pa.down; da.down_phase = c->d_down_phase; da.window = c->d_window;
+        da.est = est;
+        da.symbols = d_symbols; da.symbol_stride = symbol_stride;
+        da.sync_raw = sync_raw;
+        da.peaks = d_peaks;
+        da.tw0 = c->tw0; da.one = 1.0f;
+        da.margin = 1.0f / 8192.0f;
+        da.flag_count = flags;      // cleared by launch_demod_blocked on `st` before the fused kernel appends to it
+        da.flag_list = flags + 1;
+        da.flag_cap = da.n_windows;
+        da.stat_rechecked = c->d_stat_rechecked;
+        da.max_ctas_per_sm = 0;
+        CU(launch_demod_blocked(sf, da, c->precision, c->sm_count, st));
+        if (c->precision == PRECISION_FAST) c->stat_windows += da.n_windows;
+    }
+    if (d_metrics) {
+        FinalizeArgs fa{est, sync_raw, d_metrics, np, sf, have_sync, legacy, static_cast<int>(n_out)};
+        CU(launch_finalize(fa, st));
+    }
+    return LORA_B200_OK;
+}
+
 static int estimate_batch_locked(lora_b200_ctx* c, const float2* d_iq, size_t n_packets, size_t count,
                                  size_t packet_stride, lora_b200_pkt_metrics* d_metrics, cudaStream_t st)
 {

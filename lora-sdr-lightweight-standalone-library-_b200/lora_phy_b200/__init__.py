@@ -102,6 +102,8 @@ _SIGNATURES = {
     "lora_b200_ctx_table": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "lora_b200_demod_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                         C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "lora_b200_demod_batch_static": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                               C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lora_b200_estimate_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                            C.c_void_p, C.c_void_p]),
     "lora_b200_decode_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
@@ -244,6 +246,12 @@ class Context:
         _check(self.lib.lora_b200_demod_batch(self.h, mode, _ptr(iq), n, count, iq.stride(0), _ptr(symbols),
                                               symbols.stride(0), _ptr(peaks), _ptr(metrics), _stream()))
         return symbols[:, :n_out], metrics, peaks
+
+    def demod_batch_static(self, iq, symbols, metrics=None, peaks=None, mode=DEMOD_WORKSPACE):
+        """lora_b200_demod_batch_static: the caller passes every buffer; nothing is allocated, here or in the library."""
+        n, count = iq.shape
+        _check(self.lib.lora_b200_demod_batch_static(self.h, mode, _ptr(iq), n, count, iq.stride(0), _ptr(symbols),
+                                                     symbols.stride(0), _ptr(peaks), _ptr(metrics), _stream()))
 
     def estimate_batch(self, iq):
         import torch
