@@ -629,7 +629,7 @@ def main():
     # scaled to this launch's size; null when no capture of this SF's kernel is on file.
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             tj = json.load(f)
         if int(tj["sf"]) == dom["sf"]:
             traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"] * dom_bytes
