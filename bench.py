@@ -166,6 +166,12 @@ class Workload:
         for i in self.items:
             i["ctx"].set_kernel_timing(on)
 
+    def set_schedule(self, overlap):
+        """lora_b200_set_overlap: 2 = prepass and fused demod as items of one persistent launch (the default of the
+        library), 0 = two launches back to back."""
+        for i in self.items:
+            i["ctx"].set_overlap(overlap)
+
     def kernel_time(self):
         per_sf, tot_ms, tot_k = {}, 0.0, 0
         for i in self.items:
@@ -447,6 +453,8 @@ def main():
     ap.add_argument("--ref-packets", type=int, default=2048)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace"])
+    ap.add_argument("--schedule", default="merged", choices=["merged", "two_launch"],
+                    help="merged = prepass and demod items of one persistent launch (library default); two_launch = back to back")
     ap.add_argument("--no-int16", action="store_true", help="skip the extra int16-ingest end-to-end leg")
     ap.add_argument("--no-perf-test", action="store_true", help="skip the reference's own performance_test / rx_runner runs")
     ap.add_argument("--no-extras", action="store_true", help="skip the configs[3] stream scan and configs[4] gateway legs")
@@ -478,6 +486,8 @@ def main():
     while packets * per_packet > 0.85 * free and packets > 256:
         packets //= 2
     wl = Workload(L, torch, packets, rank)
+    merged = args.schedule == "merged"
+    wl.set_schedule(2 if merged else 0)
     gather_buf = None
     res_cat = None
     # decoded record of a packet as a gateway forwards it: chain result (length, CRC and header
@@ -522,6 +532,20 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
     k_ms, k_n, per_sf = wl.kernel_time()
+    # Outside the timed region, for continuity with the round-1 figure: the fused demod kernel on its own (two-launch
+    # schedule, 8*N + 6 algorithmic bytes per window), two steps.
+    alone = None
+    if merged:
+        wl.set_schedule(0)
+        wl.step(mode)
+        torch.cuda.synchronize()
+        wl.kernel_time()
+        for _ in range(2):
+            wl.step(mode)
+        torch.cuda.synchronize()
+        a_ms, a_n, a_per_sf = wl.kernel_time()
+        alone = (a_ms, a_n, a_per_sf, 2)
+        wl.set_schedule(2)
     wl.set_timing(False)
 
     # sanity of what was decoded (not timed): CRC-ok rate and symbol agreement with what was sent
@@ -616,20 +640,25 @@ def main():
     # Roofline.  Algorithmic bytes: 8*N*osr + 6 per window.  The dominant kernel is the demod
     # kernel of the largest SF (half of all samples of the sweep); `achieved` = its algorithmic bytes per launch over
     # its average launch duration (CUDA events recorded by the library around the launch, on the launching stream).
-    alg_bytes = sum(i["windows"] * (8 * (1 << i["sf"]) + 6) for i in wl.items) * args.steps
+    # With the merged schedule the timed launch does BOTH passes of the legacy semantics (normalisation scan + estimate
+    # items and fused demod items in one persistent kernel), so its algorithmic bytes are SURVEY 8(d)'s two-pass figure,
+    # 16*N*osr + 6 per window; ncu shows the DRAM traffic to match (profiles/r2_traffic_merged.json).
+    passes = 2 if args.mode in ("legacy", "legacy_dechirp") else 1
+    kpass = passes if merged else 1
+    win_bytes = lambda i: 8 * kpass * (1 << i["sf"]) + 6
+    alg_bytes = sum(i["windows"] * win_bytes(i) for i in wl.items) * args.steps
     achieved_all = alg_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     dom = max(wl.items, key=lambda i: per_sf[i["sf"]][0])
     dom_ms, dom_k = per_sf[dom["sf"]]
-    dom_bytes = dom["windows"] * (8 * (1 << dom["sf"]) + 6)
+    dom_bytes = dom["windows"] * win_bytes(dom)
     achieved = dom_bytes / (dom_ms / max(dom_k, 1) * 1e-3) / 1e9 if dom_ms > 0 else 0.0
-    passes = 2 if args.mode in ("legacy", "legacy_dechirp") else 1
     pipeline_bytes = sum(i["windows"] * (8 * passes * (1 << i["sf"]) + 6) for i in wl.items)
     pipeline_gbs = pipeline_bytes * args.steps / (ms_total * 1e-3) / 1e9    # per GPU: ms_total is the max over ranks
     # DRAM traffic of that kernel from the committed ncu --set full capture (bytes moved per algorithmic byte),
     # scaled to this launch's size; null when no capture of this SF's kernel is on file.
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic_merged.json" if merged else "r2_traffic.json")) as f:
             tj = json.load(f)
         if int(tj["sf"]) == dom["sf"]:
             traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"] * dom_bytes
@@ -639,7 +668,7 @@ def main():
     per_sf_out = {}
     for i in wl.items:
         ms_sf, k_sf = per_sf[i["sf"]]
-        b = i["windows"] * (8 * (1 << i["sf"]) + 6) * max(k_sf, 1)
+        b = i["windows"] * win_bytes(i) * max(k_sf, 1)
         per_sf_out[str(i["sf"])] = {"kernel_ms": round(ms_sf / max(k_sf, 1), 4),
                                     "GBps": round(b / (ms_sf * 1e-3) / 1e9, 1) if ms_sf > 0 else 0.0,
                                     "Msamples_s": round(i["samples"] * max(k_sf, 1) / (ms_sf * 1e-3) / 1e6, 1) if ms_sf > 0 else 0.0,
@@ -694,8 +723,11 @@ def main():
         "clocks": clock_info, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_source": pk_src,
-                     "kernel": f"demod_blocked_kernel<SF={dom['sf']}, fused flavour> (dechirp + rotate + FFT + argmax), "
-                               "timed with its margin-recheck launch",
+                     "kernel": (f"receive_merged_kernel<SF={dom['sf']}> (scan + estimate items and fused dechirp + rotate + FFT + "
+                                "argmax items of one persistent launch), timed with its margin-recheck launch" if merged else
+                                f"demod_blocked_kernel<SF={dom['sf']}, fused flavour> (dechirp + rotate + FFT + argmax), "
+                                "timed with its margin-recheck launch"),
+                     "algorithmic_bytes_per_window": f"{8 * kpass}*N + 6 (SURVEY.md 8d, {'two-pass legacy semantics' if kpass == 2 else 'one pass'})",
                      "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms_per_launch": dom_ms / max(dom_k, 1),
                      "traffic_source": traffic_src,
                      "all_sf": {"achieved": achieved_all, "frac": achieved_all / pk["hbm_gbs"],
@@ -705,6 +737,20 @@ def main():
                      "whole_step": {"achieved": pipeline_gbs, "frac": pipeline_gbs / pk["hbm_gbs"],
                                     "algorithmic_bytes_per_step": pipeline_bytes, "ms_per_step": ms_total / args.steps / 1.0}},
     }
+    if alone is not None:
+        a_ms, a_n, a_per_sf, a_steps = alone
+        a_bytes = sum(i["windows"] * (8 * (1 << i["sf"]) + 6) for i in wl.items) * a_steps
+        d_ms, d_k = a_per_sf[dom["sf"]]
+        d_bytes = dom["windows"] * (8 * (1 << dom["sf"]) + 6)
+        d_ach = d_bytes / (d_ms / max(d_k, 1) * 1e-3) / 1e9 if d_ms > 0 else 0.0
+        line["roofline"]["demod_kernel_alone"] = {
+            "what": "the fused demod kernel of the two-launch schedule (lora_b200_set_overlap(0)), 8*N + 6 bytes per window, "
+                    "measured over two extra steps outside the timed region: the round-1 figure's successor",
+            "achieved": d_ach, "frac": d_ach / pk["hbm_gbs"], "kernel_ms_per_launch": d_ms / max(d_k, 1),
+            "all_sf": {"achieved": a_bytes / (a_ms * 1e-3) / 1e9 if a_ms > 0 else 0.0,
+                       "frac": (a_bytes / (a_ms * 1e-3) / 1e9 if a_ms > 0 else 0.0) / pk["hbm_gbs"],
+                       "kernel_ms_per_step": a_ms / a_steps}}
+    line["config"]["schedule"] = args.schedule
     if e2e:
         line["e2e"] = e2e
     if e2e_i16:

@@ -143,8 +143,13 @@ int lora_b200_kernel_time(lora_b200_ctx* ctx, double* total_ms, unsigned long lo
 #define LORA_B200_PRECISION_FAST 0
 #define LORA_B200_PRECISION_EXACT 1
 int lora_b200_set_precision(lora_b200_ctx* ctx, int precision);
-/* Large batches (>= 256 MB of IQ) are cut into 8 sub-batches whose prepass overlaps the previous sub-batch's demod
- * kernel on internal streams; results do not depend on it.  enable = 0 runs everything on the caller's stream. */
+/* How the normalisation scan + offset estimate ("prepass") and the fused demod of lora_b200_demod_batch are scheduled;
+ * results never depend on it.
+ *   0  two launches back to back on the caller's stream
+ *   1  large legacy batches (>= 256 MB of IQ) cut into 8 sub-batches, the scan of sub-batch k+1 on an internal stream
+ *      beside the demod kernel of sub-batch k (measured slower, kept as an option)
+ *   2  one persistent launch that takes prepass items and demod items from one queue, so every SM scans some packets
+ *      while it transforms others (batches of >= 256 packets, SF7..SF12, FAST precision; otherwise as 0) */
 int lora_b200_set_overlap(lora_b200_ctx* ctx, int enable);
 /* Windows demodulated in FAST precision, and how many of them were rechecked, since the last call
  * (synchronises the device; for reporting only). */

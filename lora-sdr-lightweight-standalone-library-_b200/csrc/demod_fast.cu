@@ -16,6 +16,7 @@
 //                             are exact under PRECISION_EXACT and within 1e-4 relative under PRECISION_FAST.
 #include "demod_fast.h"
 
+#include <cstdlib>
 #include <type_traits>
 
 #include "demod_kernels.h"
@@ -78,11 +79,13 @@ struct PktParams {
     float rate, scale;
 };
 
-template <int SF>
+// COHERENT: the estimate was written by another CTA of the SAME launch (receive_merged_kernel), so it must not come
+// through the non-coherent path.
+template <int SF, bool COHERENT = false>
 PM_DEV PktParams packet_params(const BlockedDemodArgs& a, int p)
 {
     constexpr int N = 1 << SF;
-    const float4 e = __ldg(a.est + p);
+    const float4 e = COHERENT ? __ldcg(a.est + p) : __ldg(a.est + p);
     PktParams k;
     k.t_off = (int)roundf(e.y);                                                  // phy.cpp:197
     // :198  -2*pi*cfo / N; N is a power of two, so the division is the exact scaling by 1/N
@@ -188,11 +191,121 @@ struct DemodCfg {
 #ifndef LORA_V_PRE
 #define LORA_V_PRE(SF) ((SF) <= 8 ? 2 : ((SF) <= 10 ? 4 : 0))
 #endif
+// One work item of the demod kernels: a run of consecutive windows of one packet (or, LIST, one window named by the
+// recheck list), walked by the T threads of one slot.
+template <int SF, bool FAITH, bool LIST, bool OSR1, int PREMASK, bool HW, bool COHERENT = false>
+PM_DEV void demod_run(const BlockedDemodArgs& a, unsigned c, c64* S, Top* red, float* redw, const PreTw* pre, int slot, int t)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T;
+    int p, s, s_end;
+    if (LIST) { // one window, by number
+        const unsigned wn = a.flag_list[c];
+        p = a.div_total.d == 1 ? (int)wn : (int)(__umulhi(wn, a.div_total.magic) >> a.div_total.shift);
+        s = (int)(wn - (unsigned)p * (unsigned)a.total);
+        s_end = s + 1;
+    } else {    // a run of windows inside one packet
+        p = a.div_cpp.d == 1 ? (int)c : (int)(__umulhi(c, a.div_cpp.magic) >> a.div_cpp.shift);
+        s = (int)(c - (unsigned)p * a.chunks_per_packet) * (int)a.chunk_len;
+        s_end = min(s + (int)a.chunk_len, a.total);
+    }
+    const PktParams pk_ = packet_params<SF, COHERENT>(a, p);
+    const float peak_scale = pk_.scale * pk_.scale;
+    int rot_ofs = -1;
+    c64 rot[16];
+    c64 nxt[LORA_V_PREFETCH ? 16 : 1];
+    bool have_nxt = false;
+    for (; s < s_end; ++s) {
+        const WinParams q = window_params<SF, FAITH, OSR1>(a, pk_, s);
+        const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
+        const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
+        if (!LIST && LORA_V_PFDIST > 0 && t == 0) { // samples after this window: a later window of the run, or of the packet
+            const size_t span = OSR1 ? (size_t)N : (size_t)N * a.osr;
+            const size_t ahead = span * LORA_V_PFDIST;
+            const size_t left = a.count - min(a.count, q.base + ahead);
+            l2_prefetch(x + ahead, sizeof(c64) * min(span, left));
+        }
+        c64 in[16], v[16];
+        constexpr bool PF = LORA_V_PREFETCH && !FAITH && !LIST && OSR1;
+        if (PF && have_nxt) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = nxt[j];
+        } else if (OSR1) {
+            const c64* xt = x + t;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = load_sample(xt + T * j);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
+        }
+        if (PF) { // the next window of this run: its loads travel while this window is transformed
+            have_nxt = s + 1 < s_end;
+            if (have_nxt) {
+                const WinParams qn = window_params<SF, FAITH, OSR1>(a, pk_, s + 1);
+                const c64* xn = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + qn.base + t;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) nxt[j] = __ldg(xn + T * j);
+            }
+        }
+        float margin = 0.0f;
+        if (FAITH) {
+            const PrepFaith prep{a.dechirp ? a.down + q.down_ofs : nullptr, a.window, pk_.scale, true, pk_.rate, q.start, a.one};
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
+        } else {
+            if (q.down_ofs != rot_ofs) { // first window of the run, or a window whose shift was not applied
+                compute_rotors<T>(rot, a.dechirp ? a.down_phase + q.down_ofs + t : nullptr, pk_.rate, t);
+                rot_ofs = q.down_ofs;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                in[j] = cmul<false>(in[j], rot[j], 1.0f);
+                // unconditional multiply where a window is possible: a select between packed values costs moves
+                if (!OSR1) in[j] = cscale(in[j], a.window ? __ldg(a.window + t + T * j) : 1.0f);
+            }
+            // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
+            // the trusted margin widens with the magnitude of the phase
+            const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
+            margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
+        }
+        fft_blocked<SF, FAITH, PREMASK, HW>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); }, PREMASK ? pre : nullptr);
+        const int tb = HW ? HalfWarp<SF>::u_of(t) : t; // whose bins this thread holds
+        Top best{0.0f, 0, 0.0f};
+        bool owner; // the thread that reports this window
+        // measured: the winner-reports search is faster for windows of 2 or 4 warps (SF10 +3.6 %, SF11 +5 %) and
+        // slower for one warp (every warp takes the winner branch) and for eight (SF12 -6 %, longer barrier tail)
+        if (!FAITH && (T == 64 || T == 128)) {
+            owner = window_top_fast<SF, (T >= 32 ? T : 32)>(v, t, slot, redw, best, tb);
+        } else {
+            best = window_top<SF, FAITH, T>(v, t, slot, red, tb);
+            owner = t == 0;
+        }
+        if (owner) {
+            if (!FAITH) {
+                const bool trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
+                best.v *= peak_scale;
+                if (!trusted) {
+                    const unsigned k = atomicAdd(a.flag_count, 1u);
+                    if (k < a.flag_cap) a.flag_list[k] = wn;
+                }
+            }
+            if (!a.have_sync) a.symbols[(size_t)p * a.symbol_stride + s] = (uint16_t)best.i;
+            else if (s >= 2) a.symbols[(size_t)p * a.symbol_stride + (s - 2)] = (uint16_t)best.i;
+            else a.sync_raw[2 * (size_t)p + s] = (uint16_t)best.i;
+            if (a.peaks) a.peaks[wn] = best.v;
+        }
+        // No barrier here.  The peak search is itself a rendezvous of the window's threads that comes after every
+        // thread's last exchange load (warp shuffles / REDUX for T <= 32, the barrier inside window_top for
+        // T > 32), so the exchange region is already free; and red[] is not written again before the next
+        // window's first barrier, which thread 0 only reaches after it has read red[] here.
+    }
+}
+
 template <int SF, bool FAITH, bool LIST, bool OSR1>
 __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_blocked_kernel(const __grid_constant__ BlockedDemodArgs a)
 {
     using B = Blk<SF>;
-    constexpr int N = B::N, T = B::T, SLOTS = DemodCfg<SF>::SLOTS;
+    constexpr int T = B::T, SLOTS = DemodCfg<SF>::SLOTS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     c64* smem = reinterpret_cast<c64*>(smem_raw);
     __shared__ Top red[T > 32 ? kCta / 32 : 1];
@@ -208,111 +321,16 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
     const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_packets * a.chunks_per_packet;
     if (LIST && blockIdx.x == 0 && threadIdx.x == 0 && n_items) atomicAdd(a.stat_rechecked, (unsigned long long)n_items);
 
-    for (unsigned c = blockIdx.x * SLOTS + slot; c < n_items; c += gridDim.x * SLOTS) {
-        int p, s, s_end;
-        if (LIST) { // one window, by number
-            const unsigned wn = a.flag_list[c];
-            p = a.div_total.d == 1 ? (int)wn : (int)(__umulhi(wn, a.div_total.magic) >> a.div_total.shift);
-            s = (int)(wn - (unsigned)p * (unsigned)a.total);
-            s_end = s + 1;
-        } else {    // a run of windows inside one packet
-            p = a.div_cpp.d == 1 ? (int)c : (int)(__umulhi(c, a.div_cpp.magic) >> a.div_cpp.shift);
-            s = (int)(c - (unsigned)p * a.chunks_per_packet) * (int)a.chunk_len;
-            s_end = min(s + (int)a.chunk_len, a.total);
-        }
-        const PktParams pk_ = packet_params<SF>(a, p);
-        const float peak_scale = pk_.scale * pk_.scale;
-        int rot_ofs = -1;
-        c64 rot[16];
-        c64 nxt[LORA_V_PREFETCH ? 16 : 1];
-        bool have_nxt = false;
-        for (; s < s_end; ++s) {
-            const WinParams q = window_params<SF, FAITH, OSR1>(a, pk_, s);
-            const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
-            const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
-            if (!LIST && LORA_V_PFDIST > 0 && t == 0) { // samples after this window: a later window of the run, or of the packet
-                const size_t span = OSR1 ? (size_t)N : (size_t)N * a.osr;
-                const size_t ahead = span * LORA_V_PFDIST;
-                const size_t left = a.count - min(a.count, q.base + ahead);
-                l2_prefetch(x + ahead, sizeof(c64) * min(span, left));
-            }
-            c64 in[16], v[16];
-            constexpr bool PF = LORA_V_PREFETCH && !FAITH && !LIST && OSR1;
-            if (PF && have_nxt) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) in[j] = nxt[j];
-            } else if (OSR1) {
-                const c64* xt = x + t;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) in[j] = load_sample(xt + T * j);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) in[j] = __ldg(x + (size_t)(t + T * j) * a.osr);
-            }
-            if (PF) { // the next window of this run: its loads travel while this window is transformed
-                have_nxt = s + 1 < s_end;
-                if (have_nxt) {
-                    const WinParams qn = window_params<SF, FAITH, OSR1>(a, pk_, s + 1);
-                    const c64* xn = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + qn.base + t;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) nxt[j] = __ldg(xn + T * j);
-                }
-            }
-            float margin = 0.0f;
-            if (FAITH) {
-                const PrepFaith prep{a.dechirp ? a.down + q.down_ofs : nullptr, a.window, pk_.scale, true, pk_.rate, q.start, a.one};
-#pragma unroll
-                for (int j = 0; j < 16; ++j) in[j] = prep(in[j], t + T * j);
-            } else {
-                if (q.down_ofs != rot_ofs) { // first window of the run, or a window whose shift was not applied
-                    compute_rotors<T>(rot, a.dechirp ? a.down_phase + q.down_ofs + t : nullptr, pk_.rate, t);
-                    rot_ofs = q.down_ofs;
-                }
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    in[j] = cmul<false>(in[j], rot[j], 1.0f);
-                    // unconditional multiply where a window is possible: a select between packed values costs moves
-                    if (!OSR1) in[j] = cscale(in[j], a.window ? __ldg(a.window + t + T * j) : 1.0f);
-                }
-                // the reference rounds start + rate*i to float; the fast path does not reproduce that rounding, so
-                // the trusted margin widens with the magnitude of the phase
-                const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
-                margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
-            }
-            fft_blocked<SF, FAITH, PREMASK, HW>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); }, PREMASK ? pre : nullptr);
-            const int tb = HW ? HalfWarp<SF>::u_of(t) : t; // whose bins this thread holds
-            Top best{0.0f, 0, 0.0f};
-            bool owner; // the thread that reports this window
-            // measured: the winner-reports search is faster for windows of 2 or 4 warps (SF10 +3.6 %, SF11 +5 %) and
-            // slower for one warp (every warp takes the winner branch) and for eight (SF12 -6 %, longer barrier tail)
-            if (!FAITH && (T == 64 || T == 128)) {
-                owner = window_top_fast<SF, (T >= 32 ? T : 32)>(v, t, slot, redw, best, tb);
-            } else {
-                best = window_top<SF, FAITH, T>(v, t, slot, red, tb);
-                owner = t == 0;
-            }
-            if (owner) {
-                if (!FAITH) {
-                    const bool trusted = best.second < best.v * (1.0f - margin); // false for 0, NaN, Inf and near-ties
-                    best.v *= peak_scale;
-                    if (!trusted) {
-                        const unsigned k = atomicAdd(a.flag_count, 1u);
-                        if (k < a.flag_cap) a.flag_list[k] = wn;
-                    }
-                }
-                if (!a.have_sync) a.symbols[(size_t)p * a.symbol_stride + s] = (uint16_t)best.i;
-                else if (s >= 2) a.symbols[(size_t)p * a.symbol_stride + (s - 2)] = (uint16_t)best.i;
-                else a.sync_raw[2 * (size_t)p + s] = (uint16_t)best.i;
-                if (a.peaks) a.peaks[wn] = best.v;
-            }
-            // No barrier here.  The peak search is itself a rendezvous of the window's threads that comes after every
-            // thread's last exchange load (warp shuffles / REDUX for T <= 32, the barrier inside window_top for
-            // T > 32), so the exchange region is already free; and red[] is not written again before the next
-            // window's first barrier, which thread 0 only reaches after it has read red[] here.
-        }
-    }
+    for (unsigned c = blockIdx.x * SLOTS + slot; c < n_items; c += gridDim.x * SLOTS)
+        demod_run<SF, FAITH, LIST, OSR1, PREMASK, HW>(a, c, S, red, redw, pre, slot, t);
 }
 
+// Windows of the fast scan form whose loads are issued together, as a function of the 16-byte loads a thread issues
+// per window (PER: 2 at SF7, 4 at SF8, 8 from SF9 up).  Measured: two windows at a time is +5 % at SF8 and -3 % at
+// SF9 and above, so the rule keeps eight loads in flight per thread everywhere.
+#ifndef LORA_V_SCAN_WUNROLL
+#define LORA_V_SCAN_WUNROLL(PER) ((PER) >= 8 ? 1 : ((PER) >= 4 ? 2 : 4))
+#endif
 // ---- prepass: normalisation scan + offset estimate, one packet per group of TPK threads --------------------------
 template <int SF>
 struct PreCfg {
@@ -322,21 +340,13 @@ struct PreCfg {
     static constexpr int SMEM_C64 = SLOTS * Blk<SF>::WIN;
 };
 
+// The prepass of ONE packet by the TPK threads of one slot: normalisation scan, then the offset estimate; thread u == 0
+// writes est[p].  Returns with the slot's threads past their last barrier.
 template <int SF>
-__global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ PrepassArgs a)
+PM_DEV void prepass_packet(const PrepassArgs& a, int p, c64* S, Top* red, float* redf, int* redp, int slot, int u)
 {
     using B = Blk<SF>;
-    constexpr int N = B::N, T = B::T, TPK = PreCfg<SF>::TPK, SLOTS = PreCfg<SF>::SLOTS;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    c64* smem = reinterpret_cast<c64*>(smem_raw);
-    __shared__ Top red[kCta / 32];
-    __shared__ float redf[kCta / 32];
-    __shared__ int redp[kCta / 32];
-    const int slot = threadIdx.x / TPK;
-    const int u = threadIdx.x % TPK;
-    c64* S = smem + slot * B::WIN;
-    const int p = blockIdx.x * SLOTS + slot;
-    if (p >= a.n_packets) return; // whole slots leave together; slots never synchronise with each other
+    constexpr int N = B::N, T = B::T, TPK = PreCfg<SF>::TPK;
     const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride;
     // scale_from_est: the light scan kernel (scan_kernels.cu) already wrote scale and max_amp for this packet
     float4 e = a.scale_from_est ? a.est[p] : make_float4(0.0f, 0.0f, 1.0f, 0.0f);
@@ -378,6 +388,7 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
         // tracked by one packed FMA per sample (0*v + acc turns NaN as soon as any examined component is NaN or
         // Inf); in that case the packet is rescanned in the exact form, so the result never differs.
         constexpr int PER = N / (2 * TPK); // 16-byte pairs per thread per window
+        constexpr int kScanWUnroll = LORA_V_SCAN_WUNROLL(PER); // (#pragma unroll takes a constant expression, not a macro)
         bool poisoned = false;
         size_t done = 0;
         if (aligned && PER >= 1) {
@@ -397,6 +408,7 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
                     const float2 f = up(v);
                     mx = fmaxf(mx, fmaxf(fabsf(f.x), fabsf(f.y)));
                 };
+#pragma unroll kScanWUnroll
                 for (size_t w = 0; w < n_win; ++w) {
                     const ulonglong2* xw = x2 + w * (size_t)(N / 2) + u;
                     ulonglong2 v[PER > 0 ? PER : 1];
@@ -512,6 +524,103 @@ __global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ P
             e.y = __fsub_rn(avg_t, __fmul_rn(__fmul_rn(frac, (float)N), (float)a.osr));
         }
         a.est[p] = e;
+    }
+}
+
+template <int SF>
+__global__ void __maxnreg__(96) prepass_blocked_kernel(const __grid_constant__ PrepassArgs a)
+{
+    using B = Blk<SF>;
+    constexpr int TPK = PreCfg<SF>::TPK, SLOTS = PreCfg<SF>::SLOTS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    c64* smem = reinterpret_cast<c64*>(smem_raw);
+    __shared__ Top red[kCta / 32];
+    __shared__ float redf[kCta / 32];
+    __shared__ int redp[kCta / 32];
+    const int slot = threadIdx.x / TPK;
+    const int u = threadIdx.x % TPK;
+    c64* S = smem + slot * B::WIN;
+    const int p = blockIdx.x * SLOTS + slot;
+    if (p >= a.n_packets) return; // whole slots leave together; slots never synchronise with each other
+    prepass_packet<SF>(a, p, S, red, redf, redp, slot, u);
+}
+
+// ---- prepass and demod in ONE persistent launch -----------------------------------------------------------------
+// The prepass is HBM-bound (it only compares), the fused demod is issue-bound (it barely loads): run back to back they
+// leave the other resource idle, 19 + 33 ms of a 53 ms bench step.  Here both are work items of one queue that the
+// resident CTAs pull from, so at any moment some CTAs of every SM scan while the others transform.  The dependency --
+// a packet's windows need its estimate -- is carried by one word per packet: the prepass item publishes est[p] with a
+// release store, the demod item acquires it (and reads est[] through the coherent path).  The queue is ordered so that
+// the prepass of a packet group is fetched `lead` groups before the group's demod items, which makes the wait a
+// formality; it can never deadlock, because a prepass item waits for nothing and every fetched item belongs to a
+// running CTA.  Same arithmetic, same results: the two bodies are the functions the separate kernels call.
+//
+// Queue layout, in groups of kMergedGroup packets:  [prepass of groups 0..lead-1]  then for g = 0, 1, ...:
+// [prepass of group g+lead (pre_items entries)] [demod of group g (dem_items entries)].
+constexpr int kMergedGroup = 32; // packets per group: a multiple of the prepass slots per CTA of every SF
+
+#ifndef LORA_V_MERGED_CTAS
+#define LORA_V_MERGED_CTAS(SF) 2
+#endif
+
+PM_DEV unsigned ld_acquire(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+PM_DEV void st_release(unsigned* p, unsigned v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
+template <int SF, bool OSR1>
+__global__ void __launch_bounds__(kCta, LORA_V_MERGED_CTAS(SF)) receive_merged_kernel(const __grid_constant__ MergedArgs m)
+{
+    using B = Blk<SF>;
+    constexpr int T = B::T, SLOTS = DemodCfg<SF>::SLOTS, TPK = PreCfg<SF>::TPK, PSLOTS = PreCfg<SF>::SLOTS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    c64* smem = reinterpret_cast<c64*>(smem_raw);
+    __shared__ Top red[kCta / 32];
+    __shared__ float redw[2 * (kCta / 32)];
+    __shared__ float redf[kCta / 32];
+    __shared__ int redp[kCta / 32];
+    __shared__ unsigned item_s;
+    constexpr int PREMASK = LORA_V_PRE(SF);
+    constexpr bool HW = LORA_V_HALFWARP && HalfWarp<SF>::OK;
+    const unsigned head = m.lead * m.pre_items, per_group = m.pre_items + m.dem_items;
+    for (;;) {
+        if (threadIdx.x == 0) item_s = atomicAdd(m.queue, 1u);
+        __syncthreads();
+        const unsigned item = item_s;
+        __syncthreads(); // item_s is rewritten only after every thread has read it
+        if (item >= m.n_items) break;
+        bool is_pre;
+        unsigned idx, group = 0;
+        if (item < head) { is_pre = true; idx = item; }
+        else {
+            const unsigned j = item - head, r = j % per_group;
+            group = j / per_group;
+            is_pre = r < m.pre_items;
+            idx = is_pre ? (group + m.lead) * m.pre_items + r : r - m.pre_items;
+        }
+        if (is_pre) {
+            const int slot = threadIdx.x / TPK, u = threadIdx.x % TPK;
+            const long long p = (long long)idx * PSLOTS + slot;
+            if (p < m.pre.n_packets) {
+                prepass_packet<SF>(m.pre, (int)p, smem + slot * B::WIN, red, redf, redp, slot, u);
+                if (u == 0) st_release(m.ready + p, 1u); // est[p] was stored by this thread just above
+            }
+        } else {
+            const int slot = threadIdx.x / T, t = threadIdx.x % T;
+            const unsigned run = idx * SLOTS + slot, runs_per_group = kMergedGroup * m.dem.chunks_per_packet;
+            const unsigned c = group * runs_per_group + run;
+            const unsigned p = m.dem.div_cpp.d == 1 ? c : (__umulhi(c, m.dem.div_cpp.magic) >> m.dem.div_cpp.shift);
+            if (run < runs_per_group && p < m.dem.n_packets) {
+                while (ld_acquire(m.ready + p) == 0u) __nanosleep(200);
+                PreTw pre[PREMASK ? 3 : 1];
+                if (PREMASK & 2) preload_twiddles<SF, 1>(pre[1], t, m.dem.twp);
+                if (PREMASK & 4) preload_twiddles<SF, (B::NP == 3 ? 2 : 1)>(pre[2], t, m.dem.twp);
+                demod_run<SF, false, false, OSR1, PREMASK, HW, true>(m.dem, c, smem + slot * B::WIN, red, redw, pre, slot, t);
+            }
+        }
     }
 }
 
@@ -676,11 +785,70 @@ static cudaError_t launch_demod_sf(const BlockedDemodArgs& a, int precision, int
     default: return cudaErrorInvalidValue;    \
     }
 
+template <int SF, bool OSR1>
+static cudaError_t launch_merged_osr(MergedArgs m, int sm_count, cudaStream_t st)
+{
+    constexpr int SLOTS = DemodCfg<SF>::SLOTS, PSLOTS = PreCfg<SF>::SLOTS;
+    constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64; // >= the prepass's: it has no more slots than the demod
+    static_assert(kMergedGroup % PSLOTS == 0, "a group is a whole number of prepass items");
+    static int per_sm_dev[kMaxDevices] = {};
+    int& per_sm = per_sm_dev[current_device_slot()];
+    if (per_sm == 0) {
+        cudaError_t e = cudaFuncSetAttribute(receive_merged_kernel<SF, OSR1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, receive_merged_kernel<SF, OSR1>, kCta, smem);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) per_sm = 1;
+    }
+    BlockedDemodArgs& a = m.dem;
+    const long long grid = (long long)sm_count * per_sm; // persistent: exactly the CTAs that are resident together
+    const long long slots = grid * SLOTS;
+    long long cpp = (16 * slots + a.n_packets - 1) / a.n_packets; // as launch_demod_one: >= ~16 runs per slot
+    if (cpp > a.total) cpp = a.total;
+    if (cpp < 1) cpp = 1;
+    a.chunk_len = (unsigned)((a.total + cpp - 1) / cpp);
+    static const int env_chunk = getenv("LORA_B200_MERGED_CHUNK") ? atoi(getenv("LORA_B200_MERGED_CHUNK")) : 0;
+    static const double env_lead = getenv("LORA_B200_MERGED_LEAD") ? atof(getenv("LORA_B200_MERGED_LEAD")) : 2.0;
+    if (env_chunk > 0 && (unsigned)env_chunk < a.chunk_len) a.chunk_len = (unsigned)env_chunk;
+    a.chunks_per_packet = (unsigned)((a.total + a.chunk_len - 1) / a.chunk_len);
+    a.div_cpp = make_fastdiv(a.chunks_per_packet);
+    m.pre_items = kMergedGroup / PSLOTS;
+    m.dem_items = (kMergedGroup * a.chunks_per_packet + SLOTS - 1) / SLOTS;
+    const unsigned n_groups = (a.n_packets + kMergedGroup - 1) / kMergedGroup;
+    // the prepass of a group is queued ~two waves of CTAs ahead of the group's demod items
+    unsigned lead = (unsigned)((long long)(env_lead * grid + m.pre_items + m.dem_items - 1) / (m.pre_items + m.dem_items));
+    if (lead < 1) lead = 1;
+    if (lead > n_groups) lead = n_groups;
+    m.lead = lead;
+    m.n_items = lead * m.pre_items + n_groups * (m.pre_items + m.dem_items);
+    cudaError_t e = cudaMemsetAsync(m.queue, 0, sizeof(unsigned) * ((size_t)a.n_packets + 1), st); // queue head + ready[]
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(a.flag_count, 0, sizeof(unsigned), st);
+    if (e != cudaSuccess) return e;
+    receive_merged_kernel<SF, OSR1><<<(unsigned)grid, kCta, smem, st>>>(m);
+    ++g_launches;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return launch_demod_one<SF, true, true, OSR1>(a, sm_count, st); // the recheck list, as after the separate kernels
+}
+
+template <int SF>
+static cudaError_t launch_merged_sf(const MergedArgs& m, int sm_count, cudaStream_t st)
+{
+    return (m.dem.osr == 1 && m.dem.window == nullptr) ? launch_merged_osr<SF, true>(m, sm_count, st)
+                                                       : launch_merged_osr<SF, false>(m, sm_count, st);
+}
+
 cudaError_t launch_prepass_blocked(int sf, const PrepassArgs& a, cudaStream_t st) { LORA_BLOCKED_SWITCH(launch_prepass_sf, a, st) }
 
 cudaError_t launch_demod_blocked(int sf, const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st)
 {
     LORA_BLOCKED_SWITCH(launch_demod_sf, a, precision, sm_count, st)
+}
+
+cudaError_t launch_receive_merged(int sf, const MergedArgs& m, int sm_count, cudaStream_t st)
+{
+    LORA_BLOCKED_SWITCH(launch_merged_sf, m, sm_count, st)
 }
 
 } // namespace lora_b200

@@ -75,7 +75,18 @@ struct PrepassArgs {
     float one;
 };
 
+// Prepass and fused demod as work items of one persistent launch (demod_fast.cu receive_merged_kernel).
+struct MergedArgs {
+    PrepassArgs pre;
+    BlockedDemodArgs dem;   // est must be pre.est; chunking is set by the launcher
+    unsigned* queue;        // n_packets + 1 words, cleared by the launcher: [0] = queue head, [1 + p] = est[p] published
+    unsigned* ready;        // = queue + 1
+    unsigned n_items, lead, pre_items, dem_items; // set by the launcher
+};
+
 cudaError_t launch_prepass_blocked(int sf, const PrepassArgs& a, cudaStream_t st);
+// PRECISION_FAST only: queue clear, merged kernel, recheck kernel.
+cudaError_t launch_receive_merged(int sf, const MergedArgs& m, int sm_count, cudaStream_t st);
 // precision FAST: returns after queueing the fast kernel and the recheck kernel; EXACT: the faithful kernel only.
 cudaError_t launch_demod_blocked(int sf, const BlockedDemodArgs& a, int precision, int sm_count, cudaStream_t st);
 // Fills the pass-0 twiddle block from the host twiddle table.

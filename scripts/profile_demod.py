@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--precision", default="fast", choices=["fast", "exact"])
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--overlap", type=int, default=None, help="lora_b200_set_overlap value (0, 1 or 2)")
     ap.add_argument("--mode", default="legacy_dechirp", choices=["legacy_dechirp", "workspace", "legacy"])
     ap.add_argument("--lib", default=None, help="variant library built by scripts/ab_build.sh (same-box A/B timing)")
     args = ap.parse_args()
@@ -31,7 +32,7 @@ def main():
     sf = args.sf
     ctx = L.Context(sf)
     ctx.set_precision(L.PRECISION_FAST if args.precision == "fast" else L.PRECISION_EXACT)
-    ctx.set_overlap(not args.no_overlap)
+    ctx.set_overlap(args.overlap if args.overlap is not None else (0 if args.no_overlap else 1))
     cfg = L.chain_cfg(sf, 1)
     gen = torch.Generator(device="cuda").manual_seed(sf)
     pay = torch.randint(0, 256, (args.packets, 16), dtype=torch.uint8, device="cuda", generator=gen)

@@ -492,6 +492,57 @@ def test_overlapped_scan_equals_two_pass_path(env, sf, mode_name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
+@pytest.mark.parametrize("mode_name", ["dechirp", "legacy", "workspace"])
+def test_merged_launch_equals_two_launch_path(env, sf, mode_name):
+    """lora_b200_set_overlap(2): prepass items and demod items of one persistent launch (csrc/demod_fast.cu
+    receive_merged_kernel), the estimate handed from one CTA to another through a release/acquire flag per packet.
+    Symbols, sync words, cfo, time offset, max_amp and peaks must equal the two-launch path bit for bit -- with a packet
+    count that fills neither the last group of 32 nor the last work item, and with all-zero, NaN, Inf, huge and tiny
+    packets among them.  Run twice: the second call reuses the queue and the flags of the first."""
+    torch, L = env["torch"], env["L"]
+    n = 1 << sf
+    mode = {"dechirp": L.DEMOD_LEGACY_DECHIRP, "legacy": L.DEMOD_LEGACY, "workspace": L.DEMOD_WORKSPACE}[mode_name]
+    nsym = 21
+    count = (nsym + 2) * n + (n // 2 + 1 if mode_name == "legacy" else 0)
+    packets = {7: 2099, 8: 1301, 9: 1001, 10: 777, 11: 515, 12: 301}[sf]
+    ctx = L.Context(sf)
+    g = torch.Generator(device="cuda").manual_seed(1000 + sf)
+    sym = torch.randint(0, n, (packets, nsym), dtype=torch.int16, device="cuda", generator=g)
+    iq = torch.zeros((packets, count + (count & 1)), dtype=torch.complex64, device="cuda")[:, :count]
+    iq[:, :(nsym + 2) * n] = ctx.modulate_batch(sym)
+    snr = (torch.rand(packets, device="cuda", generator=g) * 30.0 - 20.0).float().contiguous()
+    ctx.awgn_batch(iq, snr, seed=sf)
+    iq[1] = 0
+    iq[2, 3 * n + 5] = complex(float("nan"), 50.0)
+    iq[3, 4 * n + 9] = complex(40.0, float("nan"))
+    iq[4, 7 * n] = complex(1.0, float("-inf"))
+    iq[5] *= 1e-3
+    iq[7] *= 1e20; iq[8] *= 1e-25
+    iq[packets - 1] *= 3.0
+    out = {}
+    for overlap in (0, 2, 2):
+        ctx.set_overlap(overlap)
+        ctx.recheck_stats()
+        s, m, pk = ctx.demod_batch(iq, mode=mode, want_peaks=True)
+        torch.cuda.synchronize()
+        got = (s.cpu().numpy().copy(), m.cpu().numpy().copy(), pk.cpu().numpy().copy(), ctx.recheck_stats())
+        if overlap == 0:
+            out[0] = got
+            continue
+        assert bits(out[0][1]) == bits(got[1]), "metrics differ"
+        assert bits(out[0][0]) == bits(got[0]), "symbols differ"
+        a, b = out[0][2], got[2]
+        assert ((a == b) | (np.isnan(a) & np.isnan(b))).all(), "peaks differ"
+        assert out[0][3] == got[3], "a different set of windows was rechecked"
+    ctx.set_overlap(0)
+    if mode_name == "dechirp":   # the mode the bench runs; the others see input their estimator was not written for
+        clean = (snr >= 0.0).cpu().numpy()
+        clean[:10] = False
+        assert (out[0][0][clean] == sym.cpu().numpy()[clean]).mean() > 0.9
+
+
+@pytest.mark.gpu
 def test_chunked_host_receive_equals_device_path(env):
     """SURVEY 8(f) rank 2, second half: lora_b200_receive_host* cut the batch into chunks whose PCIe copy overlaps the
     kernels of the chunk before (csrc/capi.cu receive_host_chunked).  With enough bytes for several chunks (and a packet
