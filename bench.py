@@ -476,6 +476,8 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        # NCCL writes its banner ("NCCL version ...") to stdout when the box sets NCCL_DEBUG: stdout is the JSON line's
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mode = L.DEMOD_LEGACY_DECHIRP if args.mode == "legacy_dechirp" else L.DEMOD_WORKSPACE
 
