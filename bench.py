@@ -591,6 +591,25 @@ def main():
            "h2d_GBps_per_gpu": e_samples * 8 * args.steps / dt / 1e9,
            "sample": f"{pe} packets per SF per GPU through lora_b200_receive_host, pinned host buffers"}
 
+    # The host limit of that leg, measured: the same pinned buffers copied to the device with NO kernels running, all
+    # ranks at once.  `e2e` cannot beat this; at N > 2 it is the host's memory system, not PCIe per GPU, that sets it.
+    for _, _, _, _, _, h in pinned[:1]:
+        wl.items[0]["iq"][:pe].copy_(h, non_blocking=True)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for (i, _, _, _, _, h) in pinned:
+            i["iq"][:pe].copy_(h, non_blocking=True)
+    torch.cuda.synchronize()
+    dc_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(dc_t, op=dist.ReduceOp.MAX)
+    copy_only = e_samples * 8 * args.steps / float(dc_t.item()) / 1e9
+    e2e["h2d_copy_only_GBps_per_gpu"] = copy_only
+    e2e["frac_of_copy_only"] = e2e["h2d_GBps_per_gpu"] / copy_only if copy_only > 0 else None
+
     # the same end-to-end leg with int16 I/Q samples: half the PCIe bytes.  Reported
     # beside `e2e`, never instead of it -- the reference-facing call takes complex<float>.
     e2e_i16 = None
