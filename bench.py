@@ -349,7 +349,7 @@ def run_reference(args, rank):
         t += dt; samples += s
     v = samples / t / 1e6
     sample = f"{packets} packets per SF (SF7-12), {samples // args.steps} samples per step, {ok} CRC-ok packets"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -357,7 +357,7 @@ def run_reference(args, rank):
                    "payload_bytes": PAYLOAD_LEN, "cr": "4/5", "header": "explicit", "crc": True, "bw_hz": 125000, "osr": 1,
                    "demod_semantics": "legacy_dechirp", "sample": sample},
         "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": sample},
-        "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
 
 def bind_to_gpu_numa_node(local):
@@ -442,7 +442,25 @@ def run_extras(args, torch, L, dist, rank, world):
 
 
 # ---- this repo's arm ---------------------------------------------------------------------------------------
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line, on the process's real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    # Libraries write to file descriptor 1 behind Python's back (NCCL prints its version banner there when the box sets
+    # NCCL_DEBUG).  Keep the real stdout for the JSON line and send everything else to stderr.
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -782,7 +800,7 @@ def main():
         line["extra"] = extras
     if cpu_error:
         line["cpu_error"] = cpu_error
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
