@@ -19,6 +19,7 @@
 #include <cstdlib>
 #include <type_traits>
 
+#include "bulk_copy.cuh"
 #include "demod_kernels.h"
 #include "exact_math.h"
 #include "window_common.cuh"
@@ -191,13 +192,39 @@ struct DemodCfg {
 #ifndef LORA_V_PRE
 #define LORA_V_PRE(SF) ((SF) <= 8 ? 2 : ((SF) <= 10 ? 4 : 0))
 #endif
+// LORA_V_TMA = 1: the fused flavour's samples are staged by ONE bulk asynchronous copy per window (cp.async.bulk,
+// completion on an mbarrier) into a per-slot buffer, issued by the slot's first thread right after the first exchange
+// barrier of the window before (every thread has consumed the buffer by then, so no extra barrier is needed); the
+// threads then read their sixteen samples with LDS instead of sixteen LDGs.  A window that does not start on a 16-byte
+// boundary is copied with one sample of slack on either side.  
+#ifndef LORA_V_TMA
+#define LORA_V_TMA 0
+#endif
+struct Stage {
+    c64* buf;                 // N + 2 samples, 16-byte aligned
+    unsigned long long* bar;  // its mbarrier
+    unsigned phase;           // parity the next wait expects
+};
+
 // One work item of the demod kernels: a run of consecutive windows of one packet (or, LIST, one window named by the
 // recheck list), walked by the T threads of one slot.
-template <int SF, bool FAITH, bool LIST, bool OSR1, int PREMASK, bool HW, bool COHERENT = false>
-PM_DEV void demod_run(const BlockedDemodArgs& a, unsigned c, c64* S, Top* red, float* redw, const PreTw* pre, int slot, int t)
+template <int SF, bool FAITH, bool LIST, bool OSR1, int PREMASK, bool HW, bool COHERENT = false, bool TMA = false>
+PM_DEV void demod_run(const BlockedDemodArgs& a, unsigned c, c64* S, Top* red, float* redw, const PreTw* pre, int slot, int t,
+                      Stage* stage = nullptr)
 {
     using B = Blk<SF>;
     constexpr int N = B::N, T = B::T;
+    static_assert(!TMA || (!FAITH && !LIST && OSR1), "staged samples: fused flavour, osr 1 only");
+    // a window can be staged when its 16-byte aligned superset stays inside the packet's samples
+    auto stage_mis = [&](const c64* xw) { return (int)((reinterpret_cast<uintptr_t>(xw) >> 3) & 1u); };
+    auto stage_ok = [&](const WinParams& w, const c64* xw) { return w.base + (size_t)N + (size_t)stage_mis(xw) <= a.count; };
+    auto stage_issue = [&](const c64* xw) {
+        const int mis = stage_mis(xw);
+        const unsigned bytes = (unsigned)((N + 2 * mis) * sizeof(c64));
+        mbar_expect_tx(stage->bar, bytes);
+        bulk_load(stage->buf, xw - mis, bytes, stage->bar);
+    };
+    bool staged_in_flight = false; // the copy of the window about to be processed has been issued
     int p, s, s_end;
     if (LIST) { // one window, by number
         const unsigned wn = a.flag_list[c];
@@ -219,7 +246,7 @@ PM_DEV void demod_run(const BlockedDemodArgs& a, unsigned c, c64* S, Top* red, f
         const WinParams q = window_params<SF, FAITH, OSR1>(a, pk_, s);
         const unsigned wn = (unsigned)p * (unsigned)a.total + (unsigned)s;
         const c64* x = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + q.base;
-        if (!LIST && LORA_V_PFDIST > 0 && t == 0) { // samples after this window: a later window of the run, or of the packet
+        if (!TMA && !LIST && LORA_V_PFDIST > 0 && t == 0) { // samples after this window: a later window of the run, or of the packet
             const size_t span = OSR1 ? (size_t)N : (size_t)N * a.osr;
             const size_t ahead = span * LORA_V_PFDIST;
             const size_t left = a.count - min(a.count, q.base + ahead);
@@ -227,7 +254,14 @@ PM_DEV void demod_run(const BlockedDemodArgs& a, unsigned c, c64* S, Top* red, f
         }
         c64 in[16], v[16];
         constexpr bool PF = LORA_V_PREFETCH && !FAITH && !LIST && OSR1;
-        if (PF && have_nxt) {
+        if (TMA && stage_ok(q, x)) {
+            if (!staged_in_flight && t == 0) stage_issue(x); // first window of the run
+            mbar_wait(stage->bar, stage->phase);
+            stage->phase ^= 1u;
+            const c64* sb = stage->buf + stage_mis(x) + t;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) in[j] = sb[T * j];
+        } else if (PF && have_nxt) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) in[j] = nxt[j];
         } else if (OSR1) {
@@ -268,6 +302,20 @@ PM_DEV void demod_run(const BlockedDemodArgs& a, unsigned c, c64* S, Top* red, f
             const float ph_max = fmaxf(fabsf(q.start), fabsf(q.start + pk_.rate * (float)N));
             margin = a.margin + 8.0f * ph_max * 1.1920929e-7f;
         }
+        if (TMA) {
+            // the next window of the run: its copy is issued behind the first exchange barrier of this one
+            const c64* xn = x;
+            bool next_ok = false;
+            if (s + 1 < s_end) {
+                const WinParams qn = window_params<SF, FAITH, OSR1>(a, pk_, s + 1);
+                xn = reinterpret_cast<const c64*>(a.iq) + (size_t)p * a.packet_stride + qn.base;
+                next_ok = stage_ok(qn, xn);
+            }
+            int syncs = 0;
+            fft_blocked<SF, FAITH, PREMASK, HW>(in, v, S, a.twp, a.tw0, t, a.one,
+                [&] { Group<T>::sync(slot); if (syncs++ == 0 && next_ok && t == 0) stage_issue(xn); }, PREMASK ? pre : nullptr);
+            staged_in_flight = next_ok;
+        } else
         fft_blocked<SF, FAITH, PREMASK, HW>(in, v, S, a.twp, a.tw0, t, a.one, [slot] { Group<T>::sync(slot); }, PREMASK ? pre : nullptr);
         const int tb = HW ? HalfWarp<SF>::u_of(t) : t; // whose bins this thread holds
         Top best{0.0f, 0, 0.0f};
@@ -321,8 +369,19 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
     const unsigned n_items = LIST ? min(*a.flag_count, a.flag_cap) : a.n_packets * a.chunks_per_packet;
     if (LIST && blockIdx.x == 0 && threadIdx.x == 0 && n_items) atomicAdd(a.stat_rechecked, (unsigned long long)n_items);
 
+    constexpr bool TMA = LORA_V_TMA && !FAITH && !LIST && OSR1;
+    static_assert(!TMA || DemodCfg<SF>::SMEM_C64 % 2 == 0, "the staging buffers start 16-byte aligned");
+    Stage stage{nullptr, nullptr, 0u};
+    if (TMA) {
+        c64* stage0 = smem + DemodCfg<SF>::SMEM_C64;                                  // after the exchange regions
+        stage.buf = stage0 + slot * (B::N + 2);
+        stage.bar = reinterpret_cast<unsigned long long*>(stage0 + SLOTS * (B::N + 2)) + slot;
+        if (t == 0) mbar_init(stage.bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        __syncthreads();
+    }
     for (unsigned c = blockIdx.x * SLOTS + slot; c < n_items; c += gridDim.x * SLOTS)
-        demod_run<SF, FAITH, LIST, OSR1, PREMASK, HW>(a, c, S, red, redw, pre, slot, t);
+        demod_run<SF, FAITH, LIST, OSR1, PREMASK, HW, false, TMA>(a, c, S, red, redw, pre, slot, t, &stage);
 }
 
 // Windows of the fast scan form whose loads are issued together, as a function of the 16-byte loads a thread issues
@@ -717,7 +776,9 @@ static cudaError_t launch_demod_one(BlockedDemodArgs a, int sm_count, cudaStream
 {
     constexpr int SLOTS = DemodCfg<SF>::SLOTS;
     // exchange regions, plus (fast flavour) 16 rotation factors per thread
-    constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64;
+    constexpr bool TMA = LORA_V_TMA && !FAITH && !LIST && OSR1;
+    constexpr size_t smem = sizeof(c64) * DemodCfg<SF>::SMEM_C64 +
+                            (TMA ? (sizeof(c64) * (Blk<SF>::N + 2) + sizeof(unsigned long long)) * SLOTS : 0);
     static int per_sm_dev[kMaxDevices] = {};
     int& per_sm = per_sm_dev[current_device_slot()];
     if (per_sm == 0) {
