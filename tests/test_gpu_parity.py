@@ -521,11 +521,26 @@ def test_merged_launch_equals_two_launch_path(env, sf, mode_name):
     iq[7] *= 1e20; iq[8] *= 1e-25
     iq[packets - 1] *= 3.0
     out = {}
+    total = count // n
+
+    def guarded(rows, cols, dtype):
+        """A [rows, cols] view in the middle of a buffer whose margins hold a pattern (compute-sanitizer is not
+        available on the GPU pool: a write outside the view shows up as a damaged margin)."""
+        pad = 4096
+        flat = torch.full((rows * cols + 2 * pad,), 23130 if dtype != torch.uint8 else 0x5A, dtype=dtype, device="cuda")
+        return flat, flat[pad:pad + rows * cols].view(rows, cols), pad
+
     for overlap in (0, 2, 2):
         ctx.set_overlap(overlap)
         ctx.recheck_stats()
-        s, m, pk = ctx.demod_batch(iq, mode=mode, want_peaks=True)
+        fs, s_buf, pad = guarded(packets, total - 2, torch.int16)
+        fm, m_buf, _ = guarded(packets, 16, torch.uint8)
+        fp, p_buf, _ = guarded(packets, total, torch.float32)
+        s_buf.zero_(); m_buf.zero_(); p_buf.zero_()
+        s, m, pk = ctx.demod_batch(iq, mode=mode, want_peaks=True, symbols=s_buf, metrics=m_buf, peaks=p_buf)
         torch.cuda.synchronize()
+        for f, fill in ((fs, 23130), (fm, 0x5A), (fp, 23130.0)):
+            assert bool((f[:pad] == fill).all()) and bool((f[-pad:] == fill).all()), "write outside an output buffer"
         got = (s.cpu().numpy().copy(), m.cpu().numpy().copy(), pk.cpu().numpy().copy(), ctx.recheck_stats())
         if overlap == 0:
             out[0] = got
