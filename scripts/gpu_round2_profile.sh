@@ -21,10 +21,14 @@ digest() { # $1 = report stem, $2 = summary name
 }
 pk() { case $1 in 7) echo 65536;; 9) echo 32768;; 12) echo 4096;; esac; }
 for sf in 7 9 12; do
-  python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --no-overlap > $O/p$sf.log 2>&1 && \
-    $NCU -k regex:demod_blocked -s 2 -c 1 -o $O/prof_sf${sf} -f python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --no-overlap > $O/ncu$sf.log 2>&1
+  python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --overlap 0 > $O/p$sf.log 2>&1 && \
+    $NCU -k regex:demod_blocked -s 2 -c 1 -o $O/prof_sf${sf} -f python scripts/profile_demod.py --sf $sf --packets $(pk $sf) --overlap 0 > $O/ncu$sf.log 2>&1
   digest prof_sf${sf} r2_ncu_sf${sf}_fast
 done
+# the merged persistent launch (library default): scan + estimate items and demod items in one kernel
+python scripts/profile_demod.py --sf 12 --packets 8192 --overlap 2 > $O/pm12.log 2>&1 && \
+  $NCU -k regex:receive_merged -s 1 -c 1 -o $O/prof_m12 -f python scripts/profile_demod.py --sf 12 --packets 8192 --overlap 2 > $O/ncum12.log 2>&1
+digest prof_m12 r2_ncu_sf12_merged
 python scripts/profile_companions.py --sf 12 --which modulate,frame,chain --packets 16384 > $O/pc12.log 2>&1 && \
   $NCU -k regex:"modulate_kernel|chain_decode_kernel" -c 3 -o $O/prof_comp -f python scripts/profile_companions.py --sf 12 --which modulate,frame,chain --packets 16384 --reps 1 > $O/ncupc.log 2>&1
 digest prof_comp r2_ncu_companions
