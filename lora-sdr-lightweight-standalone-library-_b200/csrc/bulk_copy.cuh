@@ -37,5 +37,16 @@ PM_DEV void bulk_load(void* dst, const void* src, unsigned bytes, unsigned long 
                  : "memory");
 }
 
+// One instruction asks the memory system to pull [p, p + bytes) into L2 (16-byte granules that lie fully inside the
+// range).  Issued by one thread per window for the window AFTER the one being loaded: by the time its samples are
+// wanted they come from L2 instead of HBM, without holding registers, shared memory or a barrier for them.
+PM_DEV void l2_prefetch(const void* p, size_t bytes)
+{
+    const unsigned long long a = (unsigned long long)p;
+    const unsigned long long lo = (a + 15ull) & ~15ull, hi = (a + bytes) & ~15ull;
+    if (hi > lo)
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((unsigned)(hi - lo)) : "memory");
+}
+
 } // namespace
 } // namespace lora_b200

@@ -124,17 +124,6 @@ PM_DEV WinParams window_params(const BlockedDemodArgs& a, const PktParams& k, in
     return q;
 }
 
-// One instruction asks the memory system to pull [p, p + bytes) into L2 (16-byte granules that lie fully inside the
-// range).  Issued by one thread per window for the window AFTER the one being loaded: by the time its samples are
-// wanted they come from L2 instead of HBM, without holding registers, shared memory or a barrier for them.
-PM_DEV void l2_prefetch(const void* p, size_t bytes)
-{
-    const unsigned long long a = (unsigned long long)p;
-    const unsigned long long lo = (a + 15ull) & ~15ull, hi = (a + bytes) & ~15ull;
-    if (hi > lo)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((unsigned)(hi - lo)) : "memory");
-}
-
 // Sample loads.  LORA_V_NOALLOC = 1: ld.global.nc.L1::no_allocate -- the samples are read once, so they need not
 // push the twiddle and phase tables (re-read by every window) out of L1.  Measured +1.0 / +2.9 / +0.7 % at SF9 / 11 / 12
 // (profiles/r2_ab_kernel_variants.txt); no L2 prefetch at all costs 2-3 %, a two-window prefetch distance changes nothing.

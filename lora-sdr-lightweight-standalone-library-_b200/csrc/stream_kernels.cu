@@ -13,9 +13,16 @@
 #include <cmath>
 
 #include "demod_kernels.h" // g_launches
+#include "bulk_copy.cuh"
 #include "chirp_pipeline.cuh"
 #include "exact_math.h"
 #include "window_common.cuh"
+
+// LORA_V_STREAM_PF = 1: the synchroniser asks for the window after next to be pulled into L2 -- every window is a first
+// touch of its samples.  Same-box A/B on configs[3]: +2.5 / +3 / +1 / +1.7 % at SF7 / 8 / 9 / 10 (profiles/r2_ab_stream_pf.txt).
+#ifndef LORA_V_STREAM_PF
+#define LORA_V_STREAM_PF 1
+#endif
 
 namespace lora_b200 {
 
@@ -62,6 +69,19 @@ PM_DEV int group_min(int x, int t, int slot, int* scratch /* 2 * (T/32) ints per
         for (int w = 1; w < WARPS; ++w) r = min(r, s[w]);
         return r;
     }
+}
+
+// Same-box A/B of the out-of-line rounds (profiles/r2_ab_stream_cold.txt): SF7 -2.6 %, SF8 +4.6 %, SF9 +1.7 %, SF10 -1.8 %.
+#ifndef LORA_V_STREAM_COLD_WALK
+#define LORA_V_STREAM_COLD_WALK(SF) ((SF) == 8 || (SF) == 9)
+#endif
+template <int SF>
+PM_DEV void fine_walk_rounds(int idx0, float d, unsigned Mod, int t, int slot, int* scratch, int (&idx)[16], int& carry);
+// out of line: kept out of the synchroniser's main loop, which is larger than the instruction cache likes
+template <int SF>
+__device__ __noinline__ void fine_walk_checked(int idx0, float d, unsigned Mod, int t, int slot, int* scratch, int (&idx)[16], int& carry)
+{
+    fine_walk_rounds<SF>(idx0, d, Mod, t, slot, scratch, idx, carry);
 }
 
 template <int SF>
@@ -112,6 +132,16 @@ PM_DEV void fine_walk(int idx0, float fine_err, int t, int slot, int* scratch, i
             Group<T>::sync(slot); // the scratch buffer of round 0 is written again below
         }
     }
+    if (LORA_V_STREAM_COLD_WALK(SF)) { fine_walk_checked<SF>(idx0, d, Mod, t, slot, scratch, idx, carry); return; }
+    fine_walk_rounds<SF>(idx0, d, Mod, t, slot, scratch, idx, carry);
+}
+
+// The checked rounds of the walk (about one window in eight gets here).
+template <int SF>
+PM_DEV void fine_walk_rounds(int idx0, float d, unsigned Mod, int t, int slot, int* scratch, int (&idx)[16], int& carry)
+{
+    using B = Blk<SF>;
+    constexpr int N = B::N, T = B::T;
     int base_pos = 0, base_idx = idx0;
     for (int round = 0;; ++round) {
         const int diff = base_idx - fine_step<N>(base_idx, d);                // in (-W, W)
@@ -241,6 +271,19 @@ PM_DEV Det detect_window(const StreamDetectArgs& a, const c64* __restrict__ x, c
 
 enum { FRAMESYNC, DOWNCHIRP0, DOWNCHIRP1, QUARTERCHIRP, DATASYMBOLS };
 
+// The look-ahead of FRAMESYNC (:191-204) runs the detector a second time on the same stream.  It is rare (one window in
+// a frame), so it calls an out-of-line copy: inlined twice, the detector made the kernel ~6000 instructions (96 KB), more
+// than the instruction cache holds, and `no_instruction` was the second largest stall of the kernel.
+#ifndef LORA_V_STREAM_COLD
+#define LORA_V_STREAM_COLD 1
+#endif
+template <int SF>
+__device__ __noinline__ Det detect_window_cold(const StreamDetectArgs& a, const c64* __restrict__ x, const c64* __restrict__ chirp,
+                                               int& ft, float fine_err, c64* S, const SlotShared& sh, int t, int slot)
+{
+    return detect_window<SF>(a, x, chirp, ft, fine_err, S, sh, t, slot);
+}
+
 template <int SF>
 __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_constant__ StreamDetectArgs a)
 {
@@ -275,6 +318,10 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
 
         const size_t avail = (a.count + a.osr - 1) / a.osr; // samples 0, osr, 2*osr, ... of the stream
         while (pos + 2 * (size_t)N <= avail) { // :148
+            if (LORA_V_STREAM_PF && t == 0) { // every window is a first touch of its samples: pull the one after next into L2
+                const size_t ahead = pos + 2 * (size_t)N;
+                if (ahead + (size_t)N <= avail) l2_prefetch(x + ahead * a.osr, sizeof(c64) * (size_t)N * a.osr);
+            }
             Det d = detect_window<SF>(a, x + pos * a.osr, chirp, fine_idx, fine_err, S, sh, t, slot);
             const unsigned value = (unsigned)d.value;
             const bool squelched = __fsub_rn(d.power, d.power_avg) < a.thresh; // :174
@@ -286,7 +333,8 @@ __global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_con
                 bool match1 = false;
                 if (syncd && match0) {
                     int ft = fine_idx; // the look-ahead walks a copy (:191-203) but overwrites power/powerAvg/fIndex (:204)
-                    d = detect_window<SF>(a, x + (pos + N) * a.osr, chirp, ft, fine_err, S, sh, t, slot);
+                    d = LORA_V_STREAM_COLD ? detect_window_cold<SF>(a, x + (pos + N) * a.osr, chirp, ft, fine_err, S, sh, t, slot)
+                                           : detect_window<SF>(a, x + (pos + N) * a.osr, chirp, ft, fine_err, S, sh, t, slot);
                     match1 = ((unsigned)d.value + 4) / 8 == sync_lo;
                 }
                 if (syncd && match0 && match1) {

@@ -117,7 +117,11 @@ def main():
     ap.add_argument("--symbols", type=int, default=40)
     ap.add_argument("--snr", type=float, default=10.0)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--lib", default=None, help="variant library built by scripts/ab_build.sh (same-box A/B timing)")
     args = ap.parse_args()
+    if args.lib:
+        import lora_phy_b200 as L0
+        L0.LIB_PATH = os.path.abspath(args.lib)
     if args.config3:
         return config3(args)
     import torch
