@@ -20,6 +20,10 @@
 
 // LORA_V_STREAM_PF = 1: the synchroniser asks for the window after next to be pulled into L2 -- every window is a first
 // touch of its samples.  Same-box A/B on configs[3]: +2.5 / +3 / +1 / +1.7 % at SF7 / 8 / 9 / 10 (profiles/r2_ab_stream_pf.txt).
+// Resident CTAs per SM of the synchroniser (A/B switch; 3 means 80 registers per thread).
+#ifndef LORA_V_STREAM_CTAS
+#define LORA_V_STREAM_CTAS 2
+#endif
 #ifndef LORA_V_STREAM_PF
 #define LORA_V_STREAM_PF 1
 #endif
@@ -285,7 +289,7 @@ __device__ __noinline__ Det detect_window_cold(const StreamDetectArgs& a, const 
 }
 
 template <int SF>
-__global__ void __launch_bounds__(kCta, 2) stream_detect_kernel(const __grid_constant__ StreamDetectArgs a)
+__global__ void __launch_bounds__(kCta, LORA_V_STREAM_CTAS) stream_detect_kernel(const __grid_constant__ StreamDetectArgs a)
 {
     using B = Blk<SF>;
     constexpr int N = B::N, T = B::T, SLOTS = StreamCfg<SF>::SLOTS;
