@@ -148,8 +148,10 @@ int lora_b200_set_precision(lora_b200_ctx* ctx, int precision);
  *   0  two launches back to back on the caller's stream
  *   1  large legacy batches (>= 256 MB of IQ) cut into 8 sub-batches, the scan of sub-batch k+1 on an internal stream
  *      beside the demod kernel of sub-batch k (measured slower, kept as an option)
- *   2  one persistent launch that takes prepass items and demod items from one queue, so every SM scans some packets
- *      while it transforms others (batches of >= 256 packets, SF7..SF12, FAST precision; otherwise as 0) */
+ *   2  (default) one persistent launch that takes prepass items and demod items from one queue, so every SM scans some
+ *      packets while it transforms others -- for calls of >= 600 MB of samples (and >= 256 packets, SF7..SF12, FAST
+ *      precision), where it is measured faster; smaller calls run as 0
+ *   3  as 2 without the size threshold (tests) */
 int lora_b200_set_overlap(lora_b200_ctx* ctx, int enable);
 /* Windows demodulated in FAST precision, and how many of them were rechecked, since the last call
  * (synchronises the device; for reporting only). */

@@ -244,7 +244,7 @@ extern "C" int lora_b200_set_overlap(lora_b200_ctx* c, int enable)
 {
     if (!c) return fail(LORA_B200_EINVAL, "null context");
     std::lock_guard<std::mutex> lk(c->mu);
-    c->overlap = enable < 0 ? 0 : (enable > 2 ? 2 : enable);
+    c->overlap = enable < 0 ? 0 : (enable > 3 ? 3 : enable);
     return LORA_B200_OK;
 }
 
@@ -317,7 +317,10 @@ static int demod_batch_locked(lora_b200_ctx* c, int mode, const float2* d_iq, si
                                n_packets * count * sizeof(float2) >= (size_t(256) << 20);
         // overlap == 2: prepass and fused demod as work items of ONE persistent launch (demod_fast.cu
         // receive_merged_kernel) -- the HBM-bound scan of some packets runs beside the issue-bound transform of others
-        const bool merged = c->overlap == 2 && c->precision == PRECISION_FAST && total > 0 && n_packets >= 256;
+        // Measured (profiles/r2_ab_merged_schedule.txt, small-batch table): the persistent launch wins from about 0.6 GB
+        // of samples per call (0.3 ms of work) and loses below -- its queue needs a few waves of items to overlap anything.
+        const bool merged = c->overlap >= 2 && c->precision == PRECISION_FAST && total > 0 && n_packets >= 256 &&
+                            (c->overlap == 3 || n_packets * count * sizeof(float2) >= (size_t(600) << 20));
         if (merged) CU(c->sched.reserve(sizeof(unsigned) * (std::min(n_packets, chunk_packets) + 1)));
         if (pipelined) chunk_packets = std::min(chunk_packets, (n_packets + 7) / 8);
         const size_t n_sub = (n_packets + chunk_packets - 1) / chunk_packets;

@@ -495,8 +495,8 @@ def test_overlapped_scan_equals_two_pass_path(env, sf, mode_name):
 @pytest.mark.parametrize("sf", [7, 8, 9, 10, 11, 12])
 @pytest.mark.parametrize("mode_name", ["dechirp", "legacy", "workspace"])
 def test_merged_launch_equals_two_launch_path(env, sf, mode_name):
-    """lora_b200_set_overlap(2): prepass items and demod items of one persistent launch (csrc/demod_fast.cu
-    receive_merged_kernel), the estimate handed from one CTA to another through a release/acquire flag per packet.
+    """lora_b200_set_overlap(3) (mode 2 without its size threshold): prepass items and demod items of one persistent
+    launch (csrc/demod_fast.cu receive_merged_kernel), the estimate handed from one CTA to another through a release/acquire flag per packet.
     Symbols, sync words, cfo, time offset, max_amp and peaks must equal the two-launch path bit for bit -- with a packet
     count that fills neither the last group of 32 nor the last work item, and with all-zero, NaN, Inf, huge and tiny
     packets among them.  Run twice: the second call reuses the queue and the flags of the first."""
@@ -530,7 +530,7 @@ def test_merged_launch_equals_two_launch_path(env, sf, mode_name):
         flat = torch.full((rows * cols + 2 * pad,), 23130 if dtype != torch.uint8 else 0x5A, dtype=dtype, device="cuda")
         return flat, flat[pad:pad + rows * cols].view(rows, cols), pad
 
-    for overlap in (0, 2, 2):
+    for overlap in (0, 3, 3):
         ctx.set_overlap(overlap)
         ctx.recheck_stats()
         fs, s_buf, pad = guarded(packets, total - 2, torch.int16)
@@ -550,7 +550,7 @@ def test_merged_launch_equals_two_launch_path(env, sf, mode_name):
         a, b = out[0][2], got[2]
         assert ((a == b) | (np.isnan(a) & np.isnan(b))).all(), "peaks differ"
         assert out[0][3] == got[3], "a different set of windows was rechecked"
-    ctx.set_overlap(0)
+    ctx.set_overlap(2)
     if mode_name == "dechirp":   # the mode the bench runs; the others see input their estimator was not written for
         clean = (snr >= 0.0).cpu().numpy()
         clean[:10] = False
