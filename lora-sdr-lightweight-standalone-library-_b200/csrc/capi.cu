@@ -858,7 +858,7 @@ static int modulate_locked(lora_b200_ctx* c, const uint16_t* d_symbols, size_t n
     const unsigned shift = c->cfg.sf > 4 ? c->cfg.sf - 4 : 0;   // :20-22
     a.sw0 = static_cast<uint16_t>((sync >> 4) << shift);
     a.sw1 = static_cast<uint16_t>((sync & 0x0f) << shift);
-    CU(launch_modulate(a, st));
+    CU(launch_modulate(a, c->sm_count, st));
     return LORA_B200_OK;
 }
 
@@ -1221,7 +1221,7 @@ extern "C" int lora_b200_frame_modulate_batch(lora_b200_ctx* c, const uint16_t* 
     CU(cudaSetDevice(c->device));
     FrameModArgs a{d_symbols, n_symbols, symbol_stride, reinterpret_cast<float2*>(d_iq), packet_stride,
                    static_cast<int>(n_packets), static_cast<int>(c->cfg.sf), static_cast<int>(c->cfg.osr), amplitude, sync, padding};
-    CU(launch_frame_modulate(a, static_cast<cudaStream_t>(stream)));
+    CU(launch_frame_modulate(a, c->sm_count, static_cast<cudaStream_t>(stream)));
     return LORA_B200_OK;
 }
 

@@ -20,6 +20,8 @@
 // direction.  All packets of a launch share the lengths, so every branch on them is uniform.
 #pragma once
 
+#include <cstdlib>
+
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -40,7 +42,10 @@ struct ChirpSweep {
 };
 
 // ph: this warp's two chunk buffers, [2][32][CHIRP_CHUNK + 1].  out + q * packet_stride = packet q of the warp.
-template <typename SegFn>
+// PPW = packets per warp (32, 16 or 8): the first PPW lanes run a recurrence each, all 32 lanes evaluate.  Fewer
+// packets per warp means more warps for the same batch -- the evaluation is a long dependent chain, so the kernel needs
+// a full complement of resident warps (chirp_packets_per_warp picks PPW from the batch size).
+template <int PPW = 32, typename SegFn>
 __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
                                                float amplitude, float2* out, size_t packet_stride, int warp_live,
                                                float (*ph)[32][CHIRP_CHUNK + 1])
@@ -100,17 +105,20 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
         const size_t at = k * CHIRP_CHUNK + lane; // this lane's sample in every packet of the warp
         const bool in_range = at < n_samples;
         begin_chunk();
+        constexpr int RS = 4 * 32 / PPW; // recurrence steps per iteration: the chunk's 32 spread over PPW / 4 iterations
+        static_assert(PPW == 32 || PPW == 16 || PPW == 8, "packets per warp");
 #pragma unroll 1
-        for (int q = 0; q < 32; q += 4) {
+        for (int q = 0; q < PPW; q += 4) {
             float y[4], sn[4], cs[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) y[i] = cur[q + i][lane];
+            const int r0 = (q >> 2) * RS;
             if (fast) { // the recurrence, one chunk ahead
 #pragma unroll
-                for (int i = 0; i < 4; ++i) nxt[lane][q + i] = step();
+                for (int i = 0; i < RS; ++i) nxt[lane][r0 + i] = step();
             } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) nxt[lane][q + i] = slow_step();
+                for (int i = 0; i < RS; ++i) nxt[lane][r0 + i] = slow_step();
             }
             int large = 0; // std::polar -> cosf/sinf
 #pragma unroll
@@ -132,6 +140,17 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
         }
         end_chunk();
     }
+}
+
+// Packets per warp for a batch: 32 when that still gives every SM its ~24 resident warps, else 16, else 8.
+inline int chirp_packets_per_warp(long long n_packets, int sm_count)
+{
+    static const int forced = getenv("LORA_B200_PPW") ? atoi(getenv("LORA_B200_PPW")) : 0; // experiments: 8, 16 or 32
+    if (forced == 8 || forced == 16 || forced == 32) return forced;
+    const long long want = (long long)sm_count * 24;
+    if (n_packets / 32 >= want) return 32;
+    if (n_packets / 16 >= want) return 16;
+    return 8;
 }
 
 } // namespace lora_b200

@@ -15,14 +15,15 @@ namespace lora_b200 {
 // instructions per sample), i.e. about a third of the HBM write roofline.
 constexpr int MOD_WARPS = 4;
 
+template <int PPW>
 __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a)
 {
     __shared__ float ph[MOD_WARPS][2][32][CHIRP_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int pk0 = (blockIdx.x * MOD_WARPS + warp) * 32;
+    const int pk0 = (blockIdx.x * MOD_WARPS + warp) * PPW;
     if (pk0 >= a.n_packets) return; // whole warp
     const int pk = pk0 + lane;
-    const bool live = pk < a.n_packets;
+    const bool live = lane < PPW && pk < a.n_packets;
     const int N = 1 << a.sf;
     const int step = N * a.osr;
     const double pi = 3.14159265358979323846;
@@ -39,8 +40,8 @@ __global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a
         // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
         return ChirpSegment{step, __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom), false};
     };
-    chirp_pipeline(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
-                   a.packet_stride, min(32, a.n_packets - pk0), ph[warp]);
+    chirp_pipeline<PPW>(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
+                        a.packet_stride, min(PPW, a.n_packets - pk0), ph[warp]);
 }
 
 // ---- AWGN --------------------------------------------------------------------------------------------------
@@ -79,10 +80,14 @@ __global__ void __launch_bounds__(256) awgn_kernel(AwgnArgs a)
     }
 }
 
-cudaError_t launch_modulate(const ModulateArgs& a, cudaStream_t st)
+cudaError_t launch_modulate(const ModulateArgs& a, int sm_count, cudaStream_t st)
 {
-    const int per_block = 32 * MOD_WARPS;
-    modulate_kernel<<<(a.n_packets + per_block - 1) / per_block, 32 * MOD_WARPS, 0, st>>>(a);
+    const int ppw = chirp_packets_per_warp(a.n_packets, sm_count);
+    const int per_block = ppw * MOD_WARPS;
+    const unsigned grid = (unsigned)((a.n_packets + per_block - 1) / per_block);
+    if (ppw == 32) modulate_kernel<32><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
+    else if (ppw == 16) modulate_kernel<16><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
+    else modulate_kernel<8><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
     ++g_launches;
     return cudaGetLastError();
 }

@@ -25,7 +25,7 @@ struct AwgnArgs {
     int n_packets;
 };
 
-cudaError_t launch_modulate(const ModulateArgs& a, cudaStream_t st);
+cudaError_t launch_modulate(const ModulateArgs& a, int sm_count, cudaStream_t st);
 cudaError_t launch_awgn(const AwgnArgs& a, int sm_count, cudaStream_t st);
 
 } // namespace lora_b200

@@ -431,14 +431,15 @@ __global__ void __launch_bounds__(kCta, LORA_V_STREAM_CTAS) stream_detect_kernel
 // quarter down-chirp, the data symbols; then the zero padding of :217-228.
 constexpr int FM_WARPS = 4;
 
+template <int PPW>
 __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModArgs a)
 {
     __shared__ float ph[FM_WARPS][2][32][CHIRP_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int pk0 = (blockIdx.x * FM_WARPS + warp) * 32;
+    const int pk0 = (blockIdx.x * FM_WARPS + warp) * PPW;
     if (pk0 >= a.n_packets) return; // whole warp
     const int pk = pk0 + lane;
-    const bool live = pk < a.n_packets;
+    const bool live = lane < PPW && pk < a.n_packets;
     const int N = 1 << a.sf;
     const int NN = N * a.osr;
     const double pi = 3.14159265358979323846;
@@ -448,7 +449,7 @@ __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModA
     sw.f_step = (float)__ddiv_rn(2 * pi, (double)(N * a.osr * a.osr));
     const uint16_t* sym = a.symbols + (size_t)(live ? pk : pk0) * a.symbol_stride;
     const int segments = 15 + (int)a.n_symbols; // 10 up, 2 sync, 2 down, 1/4 down, data (LoRaMod.cpp:138-208)
-    const int warp_live = min(32, a.n_packets - pk0);
+    const int warp_live = min(PPW, a.n_packets - pk0);
     auto segment = [&](int s) {
         int v = 0;
         if (s == 10) v = (int)(a.sync >> 4) * 8;          // :150
@@ -459,7 +460,7 @@ __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModA
     };
     const size_t n_samples = (size_t)(14 + a.n_symbols) * NN + NN / 4;
     float2* out = a.iq + (size_t)pk0 * a.packet_stride;
-    chirp_pipeline(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
+    chirp_pipeline<PPW>(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
     // :224-226 zero padding
     const size_t pad = (size_t)(a.padding ? a.padding : 1u) * NN; // the counter is incremented before the test (:219-221)
     for (int q = 0; q < warp_live; ++q)
@@ -534,10 +535,14 @@ cudaError_t launch_stream_detect(int sf, const StreamDetectArgs& a, int sm_count
     }
 }
 
-cudaError_t launch_frame_modulate(const FrameModArgs& a, cudaStream_t st)
+cudaError_t launch_frame_modulate(const FrameModArgs& a, int sm_count, cudaStream_t st)
 {
-    const int per_block = 32 * FM_WARPS;
-    frame_modulate_kernel<<<(a.n_packets + per_block - 1) / per_block, per_block, 0, st>>>(a);
+    const int ppw = chirp_packets_per_warp(a.n_packets, sm_count);
+    const int per_block = ppw * FM_WARPS;
+    const unsigned grid = (unsigned)((a.n_packets + per_block - 1) / per_block);
+    if (ppw == 32) frame_modulate_kernel<32><<<grid, 32 * FM_WARPS, 0, st>>>(a);
+    else if (ppw == 16) frame_modulate_kernel<16><<<grid, 32 * FM_WARPS, 0, st>>>(a);
+    else frame_modulate_kernel<8><<<grid, 32 * FM_WARPS, 0, st>>>(a);
     ++g_launches;
     return cudaGetLastError();
 }

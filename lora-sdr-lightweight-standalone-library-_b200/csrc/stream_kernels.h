@@ -64,6 +64,6 @@ void build_stream_tables(int sf, std::vector<float2>& up, std::vector<float2>& d
 size_t frame_samples(int sf, int osr, size_t n_symbols, unsigned padding);
 
 cudaError_t launch_stream_detect(int sf, const StreamDetectArgs& a, int sm_count, cudaStream_t st);
-cudaError_t launch_frame_modulate(const FrameModArgs& a, cudaStream_t st);
+cudaError_t launch_frame_modulate(const FrameModArgs& a, int sm_count, cudaStream_t st);
 
 } // namespace lora_b200
