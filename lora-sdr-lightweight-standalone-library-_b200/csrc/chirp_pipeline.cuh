@@ -41,14 +41,14 @@ struct ChirpSweep {
     float f_min, f_max, f_step; // ChirpGenerator.hpp:27-29, each evaluated in double and stored as float
 };
 
-// ph: this warp's two chunk buffers, [2][32][CHIRP_CHUNK + 1].  out + q * packet_stride = packet q of the warp.
+// ph: this warp's two chunk buffers, [2][PPW][CHIRP_CHUNK + 1].  out + q * packet_stride = packet q of the warp.
 // PPW = packets per warp (32, 16 or 8): the first PPW lanes run a recurrence each, all 32 lanes evaluate.  Fewer
 // packets per warp means more warps for the same batch -- the evaluation is a long dependent chain, so the kernel needs
 // a full complement of resident warps (chirp_packets_per_warp picks PPW from the batch size).
 template <int PPW = 32, typename SegFn>
 __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
                                                float amplitude, float2* out, size_t packet_stride, int warp_live,
-                                               float (*ph)[32][CHIRP_CHUNK + 1])
+                                               float (*ph)[PPW][CHIRP_CHUNK + 1])
 {
     const int lane = threadIdx.x & 31;
     const double pi = 3.14159265358979323846;
@@ -95,7 +95,11 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
     };
 
     begin_chunk();
-    for (int i = 0; i < CHIRP_CHUNK; ++i) ph[0][lane][i] = fast ? step() : slow_step();
+    const bool owner = PPW == 32 || lane < PPW; // lanes beyond PPW own no packet and no row of the buffers
+    for (int i = 0; i < CHIRP_CHUNK; ++i) {
+        const float v = fast ? step() : slow_step();
+        if (owner) ph[0][lane][i] = v;
+    }
     end_chunk();
     const size_t n_chunks = (n_samples + CHIRP_CHUNK - 1) / CHIRP_CHUNK;
     for (size_t k = 0; k < n_chunks; ++k) {
@@ -115,10 +119,10 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
             const int r0 = (q >> 2) * RS;
             if (fast) { // the recurrence, one chunk ahead
 #pragma unroll
-                for (int i = 0; i < RS; ++i) nxt[lane][r0 + i] = step();
+                for (int i = 0; i < RS; ++i) { const float v = step(); if (owner) nxt[lane][r0 + i] = v; }
             } else {
 #pragma unroll
-                for (int i = 0; i < RS; ++i) nxt[lane][r0 + i] = slow_step();
+                for (int i = 0; i < RS; ++i) { const float v = slow_step(); if (owner) nxt[lane][r0 + i] = v; }
             }
             int large = 0; // std::polar -> cosf/sinf
 #pragma unroll

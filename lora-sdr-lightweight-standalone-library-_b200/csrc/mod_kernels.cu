@@ -15,10 +15,14 @@ namespace lora_b200 {
 // instructions per sample), i.e. about a third of the HBM write roofline.
 constexpr int MOD_WARPS = 4;
 
+// Minimum resident CTAs per SM asked of ptxas (A/B switch: 8 means 64 registers per thread).
+#ifndef LORA_V_MOD_CTAS
+#define LORA_V_MOD_CTAS 1
+#endif
 template <int PPW>
-__global__ void __launch_bounds__(32 * MOD_WARPS) modulate_kernel(ModulateArgs a)
+__global__ void __launch_bounds__(32 * MOD_WARPS, LORA_V_MOD_CTAS) modulate_kernel(ModulateArgs a)
 {
-    __shared__ float ph[MOD_WARPS][2][32][CHIRP_CHUNK + 1];
+    __shared__ float ph[MOD_WARPS][2][PPW][CHIRP_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pk0 = (blockIdx.x * MOD_WARPS + warp) * PPW;
     if (pk0 >= a.n_packets) return; // whole warp

@@ -434,7 +434,7 @@ constexpr int FM_WARPS = 4;
 template <int PPW>
 __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModArgs a)
 {
-    __shared__ float ph[FM_WARPS][2][32][CHIRP_CHUNK + 1];
+    __shared__ float ph[FM_WARPS][2][PPW][CHIRP_CHUNK + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pk0 = (blockIdx.x * FM_WARPS + warp) * PPW;
     if (pk0 >= a.n_packets) return; // whole warp
