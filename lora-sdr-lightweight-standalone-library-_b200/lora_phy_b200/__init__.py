@@ -207,6 +207,9 @@ class Context:
         _check(self.lib.lora_b200_set_precision(self.h, int(precision)))
 
     def set_overlap(self, enable):
+        """lora_b200_set_overlap: how prepass and demod are scheduled (results never depend on it).  0 two launches,
+        1 scan of sub-batch k+1 on a second stream, 2 (default) one persistent launch for calls of >= 600 MB of
+        samples, 3 the same without the size threshold."""
         _check(self.lib.lora_b200_set_overlap(self.h, int(enable)))
 
     def recheck_stats(self):
