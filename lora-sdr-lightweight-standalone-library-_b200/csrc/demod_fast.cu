@@ -374,8 +374,9 @@ __global__ void __launch_bounds__(kCta, FAITH ? 2 : LORA_V_CTAS(SF)) demod_block
 }
 
 // Windows of the fast scan form whose loads are issued together, as a function of the 16-byte loads a thread issues
-// per window (PER: 2 at SF7, 4 at SF8, 8 from SF9 up).  Measured: two windows at a time is +5 % at SF8 and -3 % at
-// SF9 and above, so the rule keeps eight loads in flight per thread everywhere.
+// per window (PER: 2 at SF7, 4 at SF8, 8 from SF9 up).  Measured (profiles/r2_ab_merged_schedule.txt): one window at a
+// time costs 22 % at SF7 and 5 % at SF8, two at a time cost 3 % at SF9 and above, so the rule keeps eight loads in
+// flight per thread everywhere.
 #ifndef LORA_V_SCAN_WUNROLL
 #define LORA_V_SCAN_WUNROLL(PER) ((PER) >= 8 ? 1 : ((PER) >= 4 ? 2 : 4))
 #endif
