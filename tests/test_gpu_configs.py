@@ -198,9 +198,45 @@ def test_config4_gateway_step_covers_every_packet_once(env):
     import types
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
     import gateway
-    line = gateway.run(types.SimpleNamespace(channels=256, sf12_packets=2, steps=1, warmup=3, graph=False), 0, 1, None)
+    line = gateway.run(types.SimpleNamespace(channels=256, sf12_packets=2, steps=1, warmup=3, graph=False, return_state=True),
+                       0, 1, None)
     assert line["records_cover_every_channel_packet_once"] and line["config"]["channels"] == 256
     assert line["crc_ok_at_snr_ge_0dB"] > 0.99 and line["value"] > 0
+    # ... and the gathered records of a 64-channel subsample equal the oracle (the reference pipeline of
+    # tests/performance_test.cpp:103-116: caller dechirp -> lora_demodulate, then LoRaDecoder::work), two packets per
+    # channel: bytes posted, CRC flag, payload bytes, cfo and time offset, bit for bit.
+    ORC, L = env["ORC"], env["L"]
+    st = line["_state"]
+    g = st["gathered"]
+    rec_of = {}
+    for r in g[:st["counts"][0]]:
+        ch, seq = np.ascontiguousarray(r[gateway.ID_AT:gateway.REC]).view(np.uint32)
+        rec_of[(int(ch), int(seq))] = r
+    rng = np.random.default_rng(64)
+    checked = 0
+    for i in st["items"]:
+        sf, n = i["sf"], 1 << i["sf"]
+        ids = i["ident"].cpu().numpy().view(np.uint32).reshape(-1, 2)
+        channels = np.unique(ids[:, 0])
+        pick = rng.choice(channels, size=min(11, len(channels)), replace=False)
+        down = ORC.gen_chirp(n, 1, n, 0.0, True, 1.0, 0.0, 1.0)[0]
+        oc = env["orc_chain_cfg"](sf, gateway.RDD)
+        for ch in pick:
+            rows = np.nonzero(ids[:, 0] == ch)[0][:2]
+            for row in rows:
+                h_iq = i["iq"][int(row)].cpu().numpy()
+                _, so, _, mo = ORC.lora_demodulate(sf, unfused_dechirp(h_iq, down))
+                ro, bo, _ = ORC.chain_decode(oc, so)
+                if ro == -3:      # undefined in the reference itself (LoRaDecoder.cpp:381-384)
+                    continue
+                r = rec_of[(int(ch), int(ids[row, 1]))]
+                res = np.ascontiguousarray(r[0:16]).view(L.CHAIN_RESULT)[0]
+                met = np.ascontiguousarray(r[16:32]).view(L.PKT_METRICS)[0]
+                assert int(res["n_bytes"]) == ro, (sf, int(ch), int(row))
+                assert bits(r[32:32 + max(ro, 0)]) == bits(bo[:max(ro, 0)])
+                assert bits(met["cfo"]) == bits(np.float32(mo.cfo)) and bits(met["time_offset"]) == bits(np.float32(mo.time_offset))
+                checked += 1
+    assert checked >= 100
 
 
 def test_config3_stream_leg_of_the_bench(env):
