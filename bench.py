@@ -658,6 +658,36 @@ def main():
                    "h2d_bytes_per_step": int(e_samples * 4) * world, "crc_ok_packets_rank0": ok16,
                    "call": "lora_b200_receive_host_i16 (int16 I/Q, scale 2^-11), same packets quantised"}
         del i16
+    # ... and with int8 I/Q (RTL-SDR class front ends): a quarter of the PCIe bytes.  Full scale +-16 again, so the
+    # quantisation step is 1/8 -- coarse next to unit-amplitude chirps: the CRC-ok count shows what it costs.
+    e2e_i8 = None
+    if not args.no_int16:
+        q8_scale = 8.0
+        i8 = []
+        for i, h_iq, pay, res, met, h in pinned:
+            q = torch.empty((pe, i["iq"].shape[1], 2), dtype=torch.int8, pin_memory=True)
+            q.copy_(torch.view_as_real(i["iq"][:pe]).mul(q8_scale).round_().clamp_(-128, 127).to(torch.int8))
+            i8.append((i, q.numpy(), pay, res, met, q))
+        torch.cuda.synchronize()
+
+        def i8_step():
+            for i, q, pay, res, met, _ in i8:
+                i["ctx"].receive_host_i8(i["cfg"], q, scale=1.0 / q8_scale, mode=mode, payload=pay, results=res, metrics=met)
+
+        i8_step()
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            i8_step()
+        d8 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(d8, op=dist.ReduceOp.MAX)
+        ok8 = int(sum((res["crc_ok"] == 1).sum() for _, _, _, res, _, _ in i8))
+        e2e_i8 = {"value": e_samples * world * args.steps / float(d8.item()) / 1e6, "unit": "Msamples/s",
+                  "h2d_bytes_per_step": int(e_samples * 2) * world, "crc_ok_packets_rank0": ok8,
+                  "call": "lora_b200_receive_host_i8 (int8 I/Q, scale 1/8), same packets quantised"}
+        del i8
 
     # what the CPU cross-check needs from the device, then the 100+ GB of inputs make room for the extra legs
     for i in wl.items:
@@ -794,6 +824,8 @@ def main():
         line["e2e"] = e2e
     if e2e_i16:
         line["e2e_int16"] = e2e_i16
+    if e2e_i8:
+        line["e2e_int8"] = e2e_i8
     line["cpu_baseline"] = cpu
     line["host"] = {"numa": numa, "cpus": os.cpu_count()}
     if extras is not None:
