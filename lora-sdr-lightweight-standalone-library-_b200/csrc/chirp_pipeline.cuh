@@ -42,10 +42,11 @@ struct ChirpSweep {
 };
 
 // ph: this warp's two chunk buffers, [2][PPW][CHIRP_CHUNK + 1].  out + q * packet_stride = packet q of the warp.
+// SKIP_DEAD = the few-packet instantiation (n_packets < 8: the reference's per-packet API).
 // PPW = packets per warp (32, 16 or 8): the first PPW lanes run a recurrence each, all 32 lanes evaluate.  Fewer
 // packets per warp means more warps for the same batch -- the evaluation is a long dependent chain, so the kernel needs
 // a full complement of resident warps (chirp_packets_per_warp picks PPW from the batch size).
-template <int PPW = 32, typename SegFn>
+template <int PPW = 32, bool SKIP_DEAD = false, typename SegFn>
 __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
                                                float amplitude, float2* out, size_t packet_stride, int warp_live,
                                                float (*ph)[PPW][CHIRP_CHUNK + 1])
@@ -124,23 +125,37 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
 #pragma unroll
                 for (int i = 0; i < RS; ++i) { const float v = slow_step(); if (owner) nxt[lane][r0 + i] = v; }
             }
-            int large = 0; // std::polar -> cosf/sinf
+            // Packets beyond the warp's last live one are not evaluated: a single-packet call -- the reference's
+            // per-packet API -- would otherwise pay for PPW packets (the recurrence above still advances).  The full
+            // group of four keeps its own straight-line code, and batches (SKIP_DEAD = false) compile to exactly that:
+            // guards inside the group cost the batched path a quarter of its rate, the extra branch alone 9 %.
+            const int nlive = SKIP_DEAD ? warp_live - q : 4; // warp-uniform; a compile-time 4 for batches
+            if (nlive >= 4) {
+                int large = 0; // std::polar -> cosf/sinf
 #pragma unroll
-            for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
-            if (__all_sync(0xffffffffu, large == 0)) {
+                for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
+                if (__all_sync(0xffffffffu, large == 0)) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
-            } else if (__all_sync(0xffffffffu, large == 4)) {
+                    for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
+                } else if (__all_sync(0xffffffffu, large == 4)) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
-            } else {
+                    for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
+                } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
+                    for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (in_range && q + i < warp_live)
+                        out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, cs[i]), __fmul_rn(amplitude, sn[i]));
+            } else if (nlive > 0) { // the ragged last group: one packet at a time, both reductions computed
+#pragma unroll 1
+                for (int i = 0; i < nlive; ++i) {
+                    float s1, c1;
+                    xm_sincosf_paths(y[i], &s1, &c1, 1, 1);
+                    if (in_range) out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, c1), __fmul_rn(amplitude, s1));
+                }
             }
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (in_range && q + i < warp_live)
-                    out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, cs[i]), __fmul_rn(amplitude, sn[i]));
         }
         end_chunk();
     }

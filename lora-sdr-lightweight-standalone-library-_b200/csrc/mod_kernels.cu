@@ -19,7 +19,7 @@ constexpr int MOD_WARPS = 4;
 #ifndef LORA_V_MOD_CTAS
 #define LORA_V_MOD_CTAS 1
 #endif
-template <int PPW>
+template <int PPW, bool FEW = false>
 __global__ void __launch_bounds__(32 * MOD_WARPS, LORA_V_MOD_CTAS) modulate_kernel(ModulateArgs a)
 {
     __shared__ float ph[MOD_WARPS][2][PPW][CHIRP_CHUNK + 1];
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(32 * MOD_WARPS, LORA_V_MOD_CTAS) modulate_kern
         // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
         return ChirpSegment{step, __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom), false};
     };
-    chirp_pipeline<PPW>(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
+    chirp_pipeline<PPW, FEW>(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
                         a.packet_stride, min(PPW, a.n_packets - pk0), ph[warp]);
 }
 
@@ -91,7 +91,8 @@ cudaError_t launch_modulate(const ModulateArgs& a, int sm_count, cudaStream_t st
     const unsigned grid = (unsigned)((a.n_packets + per_block - 1) / per_block);
     if (ppw == 32) modulate_kernel<32><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
     else if (ppw == 16) modulate_kernel<16><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
-    else modulate_kernel<8><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
+    else if (a.n_packets >= 8) modulate_kernel<8><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
+    else modulate_kernel<8, true><<<grid, 32 * MOD_WARPS, 0, st>>>(a); // a packet or a few: lora_modulate of the per-packet API
     ++g_launches;
     return cudaGetLastError();
 }

@@ -431,7 +431,7 @@ __global__ void __launch_bounds__(kCta, LORA_V_STREAM_CTAS) stream_detect_kernel
 // quarter down-chirp, the data symbols; then the zero padding of :217-228.
 constexpr int FM_WARPS = 4;
 
-template <int PPW>
+template <int PPW, bool FEW = false>
 __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModArgs a)
 {
     __shared__ float ph[FM_WARPS][2][PPW][CHIRP_CHUNK + 1];
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModA
     };
     const size_t n_samples = (size_t)(14 + a.n_symbols) * NN + NN / 4;
     float2* out = a.iq + (size_t)pk0 * a.packet_stride;
-    chirp_pipeline<PPW>(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
+    chirp_pipeline<PPW, FEW>(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
     // :224-226 zero padding
     const size_t pad = (size_t)(a.padding ? a.padding : 1u) * NN; // the counter is incremented before the test (:219-221)
     for (int q = 0; q < warp_live; ++q)
@@ -542,7 +542,8 @@ cudaError_t launch_frame_modulate(const FrameModArgs& a, int sm_count, cudaStrea
     const unsigned grid = (unsigned)((a.n_packets + per_block - 1) / per_block);
     if (ppw == 32) frame_modulate_kernel<32><<<grid, 32 * FM_WARPS, 0, st>>>(a);
     else if (ppw == 16) frame_modulate_kernel<16><<<grid, 32 * FM_WARPS, 0, st>>>(a);
-    else frame_modulate_kernel<8><<<grid, 32 * FM_WARPS, 0, st>>>(a);
+    else if (a.n_packets >= 8) frame_modulate_kernel<8><<<grid, 32 * FM_WARPS, 0, st>>>(a);
+    else frame_modulate_kernel<8, true><<<grid, 32 * FM_WARPS, 0, st>>>(a);
     ++g_launches;
     return cudaGetLastError();
 }
