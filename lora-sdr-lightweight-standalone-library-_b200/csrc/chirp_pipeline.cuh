@@ -42,11 +42,11 @@ struct ChirpSweep {
 };
 
 // ph: this warp's two chunk buffers, [2][PPW][CHIRP_CHUNK + 1].  out + q * packet_stride = packet q of the warp.
-// SKIP_DEAD = the few-packet instantiation (n_packets < 8: the reference's per-packet API).
+// (Calls of fewer than 8 packets -- the reference's per-packet API -- use chirp_one_packet below instead.)
 // PPW = packets per warp (32, 16 or 8): the first PPW lanes run a recurrence each, all 32 lanes evaluate.  Fewer
 // packets per warp means more warps for the same batch -- the evaluation is a long dependent chain, so the kernel needs
 // a full complement of resident warps (chirp_packets_per_warp picks PPW from the batch size).
-template <int PPW = 32, bool SKIP_DEAD = false, typename SegFn>
+template <int PPW = 32, typename SegFn>
 __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
                                                float amplitude, float2* out, size_t packet_stride, int warp_live,
                                                float (*ph)[PPW][CHIRP_CHUNK + 1])
@@ -125,39 +125,126 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
 #pragma unroll
                 for (int i = 0; i < RS; ++i) { const float v = slow_step(); if (owner) nxt[lane][r0 + i] = v; }
             }
-            // Packets beyond the warp's last live one are not evaluated: a single-packet call -- the reference's
-            // per-packet API -- would otherwise pay for PPW packets (the recurrence above still advances).  The full
-            // group of four keeps its own straight-line code, and batches (SKIP_DEAD = false) compile to exactly that:
-            // guards inside the group cost the batched path a quarter of its rate, the extra branch alone 9 %.
-            const int nlive = SKIP_DEAD ? warp_live - q : 4; // warp-uniform; a compile-time 4 for batches
-            if (nlive >= 4) {
-                int large = 0; // std::polar -> cosf/sinf
+            int large = 0; // std::polar -> cosf/sinf
 #pragma unroll
-                for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
-                if (__all_sync(0xffffffffu, large == 0)) {
+            for (int i = 0; i < 4; ++i) large += xm_is_large_arg(y[i]);
+            if (__all_sync(0xffffffffu, large == 0)) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
-                } else if (__all_sync(0xffffffffu, large == 4)) {
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 0);
+            } else if (__all_sync(0xffffffffu, large == 4)) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
-                } else {
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 0, 1);
+            } else {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (in_range && q + i < warp_live)
-                        out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, cs[i]), __fmul_rn(amplitude, sn[i]));
-            } else if (nlive > 0) { // the ragged last group: one packet at a time, both reductions computed
-#pragma unroll 1
-                for (int i = 0; i < nlive; ++i) {
-                    float s1, c1;
-                    xm_sincosf_paths(y[i], &s1, &c1, 1, 1);
-                    if (in_range) out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, c1), __fmul_rn(amplitude, s1));
-                }
+                for (int i = 0; i < 4; ++i) xm_sincosf_paths(y[i], &sn[i], &cs[i], 1, 1);
             }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (in_range && q + i < warp_live)
+                    out[(size_t)(q + i) * packet_stride + at] = make_float2(__fmul_rn(amplitude, cs[i]), __fmul_rn(amplitude, sn[i]));
         }
         end_chunk();
+    }
+}
+
+// ---- one packet per CTA: the per-packet API of the reference (lora_modulate called for one packet) -----------------
+// With a single packet the recurrence IS the critical path (three dependent float operations per sample), and in the
+// warp-per-packets engine above it shares one instruction stream with a ~100-instruction sincos per chunk.  Here a CTA
+// of four warps takes one packet: warp 0 only runs the recurrence -- all 32 lanes redundantly, lane l keeping sample l of
+// the chunk, so no transpose is needed -- and hands each chunk of 32 phases to one of three evaluating warps through a
+// ring of six slots in shared memory.  Hand-over is the producer/consumer form of the named barriers: the producer
+// `bar.arrive`s on a slot's "full" barrier after storing, the consumer `bar.sync`s on it before loading, and the other
+// way round on the slot's "empty" barrier.  Per chunk the packet then costs max(recurrence, evaluation / 3).
+constexpr int CHIRP_ONE_WARPS = 4, CHIRP_ONE_SLOTS = 6; // slot k % 6 is always evaluated by warp 1 + k % 3
+
+__device__ __forceinline__ void chirp_bar_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void chirp_bar_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+
+// ring: [CHIRP_ONE_SLOTS][32] floats of shared memory.  Called by all 128 threads of the CTA.
+template <typename SegFn>
+__device__ __forceinline__ void chirp_one_packet(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
+                                                 float amplitude, float2* out, float (*ring)[32])
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t n_chunks = (n_samples + CHIRP_CHUNK - 1) / CHIRP_CHUNK;
+    constexpr int FULL = 1, EMPTY = 1 + CHIRP_ONE_SLOTS; // barrier ids 1..6 and 7..12 (0 is __syncthreads)
+    if (warp == 0) {
+        // the recurrence of chirp_pipeline, every lane running the same packet
+        const double pi = 3.14159265358979323846;
+        const float span = __fsub_rn(sw.f_max, sw.f_min);
+        float f = 0.0f, phase = 0.0f;
+        int s = 0, j = 0, len = 0;
+        bool down = false;
+        auto load_segment = [&]() {
+            if (s < n_segments) {
+                const ChirpSegment g = segment(s);
+                len = g.len;
+                down = g.down;
+                f = __fadd_rn(sw.f_min, g.f0);
+            }
+        };
+        auto step = [&]() -> float { // ChirpGenerator.hpp:33-46
+            f = __fadd_rn(f, sw.f_step);
+            if (f > sw.f_max) f = __fsub_rn(f, span);
+            phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
+            return phase;
+        };
+        auto finish_segment = [&]() { // :48
+            const double pd = (double)phase;
+            phase = (float)__dsub_rn(pd, __dmul_rn(__dmul_rn(floor(__ddiv_rn(pd, 2 * pi)), 2.0), pi));
+            j = 0;
+            ++s;
+            load_segment();
+        };
+        auto slow_step = [&]() -> float {
+            if (s >= n_segments) return 0.0f;
+            const float r = step();
+            if (++j == len) finish_segment();
+            return r;
+        };
+        load_segment();
+        while (s < n_segments && len == 0) finish_segment();
+        for (size_t k = 0; k < n_chunks; ++k) {
+            const int slot = (int)(k % CHIRP_ONE_SLOTS);
+            float mine = 0.0f;
+            if (s < n_segments && len - j >= CHIRP_CHUNK) { // the chunk lies inside one chirp
+                // The frequency wraps once per chirp.  When it provably cannot within this chunk -- the float sum after
+                // 32 steps stays below f + 40 * f_step -- the compare-and-subtract leaves the dependency chain.
+                if (__fadd_rn(f, __fmul_rn(40.0f, sw.f_step)) < sw.f_max) {
+#pragma unroll
+                    for (int i = 0; i < CHIRP_CHUNK; ++i) {
+                        f = __fadd_rn(f, sw.f_step);
+                        phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
+                        if (i == lane) mine = phase;
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < CHIRP_CHUNK; ++i) { const float v = step(); if (i == lane) mine = v; }
+                }
+                j += CHIRP_CHUNK;
+                if (j == len) finish_segment();
+            } else {
+#pragma unroll 1
+                for (int i = 0; i < CHIRP_CHUNK; ++i) { const float v = slow_step(); if (i == lane) mine = v; }
+            }
+            if (k >= (size_t)CHIRP_ONE_SLOTS) chirp_bar_sync(EMPTY + slot); // its previous occupant has been read
+            ring[slot][lane] = mine;
+            chirp_bar_arrive(FULL + slot);
+        }
+    } else {
+        for (size_t k = (size_t)(warp - 1); k < n_chunks; k += CHIRP_ONE_WARPS - 1) {
+            const int slot = (int)(k % CHIRP_ONE_SLOTS);
+            chirp_bar_sync(FULL + slot);
+            const float y = ring[slot][lane];
+            chirp_bar_arrive(EMPTY + slot);
+            float sn, cs; // std::polar -> cosf/sinf, one warp-uniform choice of range reduction
+            const int large = xm_is_large_arg(y);
+            if (__all_sync(0xffffffffu, large == 0)) xm_sincosf_paths(y, &sn, &cs, 1, 0);
+            else if (__all_sync(0xffffffffu, large == 1)) xm_sincosf_paths(y, &sn, &cs, 0, 1);
+            else xm_sincosf_paths(y, &sn, &cs, 1, 1);
+            const size_t at = k * CHIRP_CHUNK + lane;
+            if (at < n_samples) out[at] = make_float2(__fmul_rn(amplitude, cs), __fmul_rn(amplitude, sn));
+        }
     }
 }
 

@@ -19,7 +19,7 @@ constexpr int MOD_WARPS = 4;
 #ifndef LORA_V_MOD_CTAS
 #define LORA_V_MOD_CTAS 1
 #endif
-template <int PPW, bool FEW = false>
+template <int PPW>
 __global__ void __launch_bounds__(32 * MOD_WARPS, LORA_V_MOD_CTAS) modulate_kernel(ModulateArgs a)
 {
     __shared__ float ph[MOD_WARPS][2][PPW][CHIRP_CHUNK + 1];
@@ -44,8 +44,31 @@ __global__ void __launch_bounds__(32 * MOD_WARPS, LORA_V_MOD_CTAS) modulate_kern
         // LoRaMod.cpp:24,29,36: ((2*pi_f * v) * bw_scale) / (N * osr)
         return ChirpSegment{step, __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom), false};
     };
-    chirp_pipeline<PPW, FEW>(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
+    chirp_pipeline<PPW>(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk0 * a.packet_stride,
                         a.packet_stride, min(PPW, a.n_packets - pk0), ph[warp]);
+}
+
+// lora_modulate of ONE packet per CTA (the reference's per-packet API): chirp_one_packet of chirp_pipeline.cuh.
+__global__ void __launch_bounds__(32 * CHIRP_ONE_WARPS) modulate_few_kernel(ModulateArgs a)
+{
+    __shared__ float ring[CHIRP_ONE_SLOTS][32];
+    const int pk = blockIdx.x;
+    const int N = 1 << a.sf;
+    const int step = N * a.osr;
+    const double pi = 3.14159265358979323846;
+    ChirpSweep sw;
+    sw.f_min = (float)__ddiv_rn(__dmul_rn(-pi, (double)a.bw_scale), (double)a.osr);
+    sw.f_max = (float)__ddiv_rn(__dmul_rn(pi, (double)a.bw_scale), (double)a.osr);
+    sw.f_step = (float)__ddiv_rn(__dmul_rn(2 * pi, (double)a.bw_scale), (double)(N * a.osr * a.osr));
+    const float pi_f = 3.14159274101257324f;
+    const float denom = __fmul_rn((float)N, (float)a.osr);
+    const uint16_t* sym = a.symbols + (size_t)pk * a.symbol_stride;
+    const int total = (int)a.n_symbols + 2;
+    auto segment = [&](int s) {
+        const unsigned v = s == 0 ? a.sw0 : s == 1 ? a.sw1 : (unsigned)sym[s - 2];
+        return ChirpSegment{step, __fdiv_rn(__fmul_rn(__fmul_rn(2.0f * pi_f, (float)v), a.bw_scale), denom), false};
+    };
+    chirp_one_packet(segment, total, (size_t)total * step, sw, a.amplitude, a.iq + (size_t)pk * a.packet_stride, ring);
 }
 
 // ---- AWGN --------------------------------------------------------------------------------------------------
@@ -86,13 +109,17 @@ __global__ void __launch_bounds__(256) awgn_kernel(AwgnArgs a)
 
 cudaError_t launch_modulate(const ModulateArgs& a, int sm_count, cudaStream_t st)
 {
+    if (a.n_packets < 8) { // a packet or a few: one CTA each, recurrence and evaluation on different warps
+        modulate_few_kernel<<<(unsigned)a.n_packets, 32 * CHIRP_ONE_WARPS, 0, st>>>(a);
+        ++g_launches;
+        return cudaGetLastError();
+    }
     const int ppw = chirp_packets_per_warp(a.n_packets, sm_count);
     const int per_block = ppw * MOD_WARPS;
     const unsigned grid = (unsigned)((a.n_packets + per_block - 1) / per_block);
     if (ppw == 32) modulate_kernel<32><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
     else if (ppw == 16) modulate_kernel<16><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
-    else if (a.n_packets >= 8) modulate_kernel<8><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
-    else modulate_kernel<8, true><<<grid, 32 * MOD_WARPS, 0, st>>>(a); // a packet or a few: lora_modulate of the per-packet API
+    else modulate_kernel<8><<<grid, 32 * MOD_WARPS, 0, st>>>(a);
     ++g_launches;
     return cudaGetLastError();
 }

@@ -431,7 +431,7 @@ __global__ void __launch_bounds__(kCta, LORA_V_STREAM_CTAS) stream_detect_kernel
 // quarter down-chirp, the data symbols; then the zero padding of :217-228.
 constexpr int FM_WARPS = 4;
 
-template <int PPW, bool FEW = false>
+template <int PPW>
 __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModArgs a)
 {
     __shared__ float ph[FM_WARPS][2][PPW][CHIRP_CHUNK + 1];
@@ -460,11 +460,39 @@ __global__ void __launch_bounds__(32 * FM_WARPS) frame_modulate_kernel(FrameModA
     };
     const size_t n_samples = (size_t)(14 + a.n_symbols) * NN + NN / 4;
     float2* out = a.iq + (size_t)pk0 * a.packet_stride;
-    chirp_pipeline<PPW, FEW>(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
+    chirp_pipeline<PPW>(segment, segments, n_samples, sw, a.amplitude, out, a.packet_stride, warp_live, ph[warp]);
     // :224-226 zero padding
     const size_t pad = (size_t)(a.padding ? a.padding : 1u) * NN; // the counter is incremented before the test (:219-221)
     for (int q = 0; q < warp_live; ++q)
         for (size_t i = lane; i < pad; i += 32) out[(size_t)q * a.packet_stride + n_samples + i] = make_float2(0.0f, 0.0f);
+}
+
+// One frame per CTA (a caller generating frames one at a time): chirp_one_packet of chirp_pipeline.cuh.
+__global__ void __launch_bounds__(32 * CHIRP_ONE_WARPS) frame_modulate_few_kernel(FrameModArgs a)
+{
+    __shared__ float ring[CHIRP_ONE_SLOTS][32];
+    const int pk = blockIdx.x;
+    const int N = 1 << a.sf;
+    const int NN = N * a.osr;
+    const double pi = 3.14159265358979323846;
+    ChirpSweep sw;
+    sw.f_min = (float)__ddiv_rn(-pi, (double)a.osr);
+    sw.f_max = (float)__ddiv_rn(pi, (double)a.osr);
+    sw.f_step = (float)__ddiv_rn(2 * pi, (double)(N * a.osr * a.osr));
+    const uint16_t* sym = a.symbols + (size_t)pk * a.symbol_stride;
+    const int segments = 15 + (int)a.n_symbols;
+    auto segment = [&](int s) {
+        int v = 0;
+        if (s == 10) v = (int)(a.sync >> 4) * 8;
+        else if (s == 11) v = (int)(a.sync & 0xfu) * 8;
+        else if (s >= 15) v = sym[s - 15];
+        return ChirpSegment{s == 14 ? NN / 4 : NN, (float)__ddiv_rn(__dmul_rn(2 * pi, (double)v), (double)NN), s >= 12 && s < 15};
+    };
+    const size_t n_samples = (size_t)(14 + a.n_symbols) * NN + NN / 4;
+    float2* out = a.iq + (size_t)pk * a.packet_stride;
+    const size_t pad = (size_t)(a.padding ? a.padding : 1u) * NN;
+    for (size_t i = threadIdx.x; i < pad; i += blockDim.x) out[n_samples + i] = make_float2(0.0f, 0.0f); // :224-226
+    chirp_one_packet(segment, segments, n_samples, sw, a.amplitude, out, ring);
 }
 
 template <int SF>
@@ -537,13 +565,17 @@ cudaError_t launch_stream_detect(int sf, const StreamDetectArgs& a, int sm_count
 
 cudaError_t launch_frame_modulate(const FrameModArgs& a, int sm_count, cudaStream_t st)
 {
+    if (a.n_packets < 8) {
+        frame_modulate_few_kernel<<<(unsigned)a.n_packets, 32 * CHIRP_ONE_WARPS, 0, st>>>(a);
+        ++g_launches;
+        return cudaGetLastError();
+    }
     const int ppw = chirp_packets_per_warp(a.n_packets, sm_count);
     const int per_block = ppw * FM_WARPS;
     const unsigned grid = (unsigned)((a.n_packets + per_block - 1) / per_block);
     if (ppw == 32) frame_modulate_kernel<32><<<grid, 32 * FM_WARPS, 0, st>>>(a);
     else if (ppw == 16) frame_modulate_kernel<16><<<grid, 32 * FM_WARPS, 0, st>>>(a);
-    else if (a.n_packets >= 8) frame_modulate_kernel<8><<<grid, 32 * FM_WARPS, 0, st>>>(a);
-    else frame_modulate_kernel<8, true><<<grid, 32 * FM_WARPS, 0, st>>>(a);
+    else frame_modulate_kernel<8><<<grid, 32 * FM_WARPS, 0, st>>>(a);
     ++g_launches;
     return cudaGetLastError();
 }
