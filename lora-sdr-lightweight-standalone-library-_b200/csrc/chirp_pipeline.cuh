@@ -152,22 +152,29 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
 // warp-per-packets engine above it shares one instruction stream with a ~100-instruction sincos per chunk.  Here a CTA
 // of four warps takes one packet: warp 0 only runs the recurrence -- all 32 lanes redundantly, lane l keeping sample l of
 // the chunk, so no transpose is needed -- and hands each chunk of 32 phases to one of three evaluating warps through a
-// ring of six slots in shared memory.  Hand-over is the producer/consumer form of the named barriers: the producer
+// ring of one slot per evaluating warp in shared memory.  Hand-over is the producer/consumer form of the named barriers: the producer
 // `bar.arrive`s on a slot's "full" barrier after storing, the consumer `bar.sync`s on it before loading, and the other
 // way round on the slot's "empty" barrier.  Per chunk the packet then costs max(recurrence, evaluation / 3).
-constexpr int CHIRP_ONE_WARPS = 4, CHIRP_ONE_SLOTS = 6; // slot k % 6 is always evaluated by warp 1 + k % 3
+// Warps per packet: the recurrence warp plus the evaluating ones.  Measured: 8 is no faster than 4 (2326 vs 2172 us for
+// an SF12 packet) -- the recurrence warp is the limit, not the evaluation.
+#ifndef LORA_V_ONE_WARPS
+#define LORA_V_ONE_WARPS 4
+#endif
+// one slot per evaluating warp: slot k % SLOTS is always evaluated by warp 1 + k % SLOTS (2 * SLOTS barrier ids <= 14)
+constexpr int CHIRP_ONE_WARPS = LORA_V_ONE_WARPS, CHIRP_ONE_SLOTS = LORA_V_ONE_WARPS - 1;
 
 __device__ __forceinline__ void chirp_bar_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void chirp_bar_arrive(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
 
-// ring: [CHIRP_ONE_SLOTS][32] floats of shared memory.  Called by all 128 threads of the CTA.
+// ring: [CHIRP_ONE_SLOTS][32] floats of shared memory.  Called by all 32 * CHIRP_ONE_WARPS threads of the CTA.
 template <typename SegFn>
 __device__ __forceinline__ void chirp_one_packet(const SegFn& segment, int n_segments, size_t n_samples, const ChirpSweep sw,
                                                  float amplitude, float2* out, float (*ring)[32])
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t n_chunks = (n_samples + CHIRP_CHUNK - 1) / CHIRP_CHUNK;
-    constexpr int FULL = 1, EMPTY = 1 + CHIRP_ONE_SLOTS; // barrier ids 1..6 and 7..12 (0 is __syncthreads)
+    constexpr int FULL = 1, EMPTY = 1 + CHIRP_ONE_SLOTS; // barrier ids 1..SLOTS and SLOTS+1..2*SLOTS (0 is __syncthreads)
+    static_assert(2 * CHIRP_ONE_SLOTS <= 14 && CHIRP_ONE_SLOTS >= 1, "named barriers 1..15");
     if (warp == 0) {
         // the recurrence of chirp_pipeline, every lane running the same packet
         const double pi = 3.14159265358979323846;
