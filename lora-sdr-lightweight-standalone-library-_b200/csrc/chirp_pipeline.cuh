@@ -156,7 +156,9 @@ __device__ __forceinline__ void chirp_pipeline(const SegFn& segment, int n_segme
 // `bar.arrive`s on a slot's "full" barrier after storing, the consumer `bar.sync`s on it before loading, and the other
 // way round on the slot's "empty" barrier.  Per chunk the packet then costs max(recurrence, evaluation / 3).
 // Warps per packet: the recurrence warp plus the evaluating ones.  Measured: 8 is no faster than 4 (2326 vs 2172 us for
-// an SF12 packet) -- the recurrence warp is the limit, not the evaluation.
+// an SF12 packet), and with the evaluation compiled out the time does not change either: the recurrence warp is the
+// limit -- ~15 cycles of the nominal clock per sample for a 4-instruction step, i.e. a single small kernel on an
+// otherwise idle GPU runs at the idle clock.
 #ifndef LORA_V_ONE_WARPS
 #define LORA_V_ONE_WARPS 4
 #endif
@@ -182,18 +184,27 @@ __device__ __forceinline__ void chirp_one_packet(const SegFn& segment, int n_seg
         float f = 0.0f, phase = 0.0f;
         int s = 0, j = 0, len = 0;
         bool down = false;
+        unsigned flip = 0u; // sign bit applied to f before it enters the phase sum
+        // The descriptor of a chirp (a symbol read from global memory and a division) is fetched one chirp ahead: on
+        // this warp's critical path its latency would cost as much as a chunk at SF7.
+        ChirpSegment ahead = n_segments > 0 ? segment(0) : ChirpSegment{0, 0.0f, false};
         auto load_segment = [&]() {
             if (s < n_segments) {
-                const ChirpSegment g = segment(s);
+                const ChirpSegment g = ahead;
                 len = g.len;
                 down = g.down;
+                flip = down ? 0x80000000u : 0u;
                 f = __fadd_rn(sw.f_min, g.f0);
+                if (s + 1 < n_segments) ahead = segment(s + 1);
             }
         };
+        // phase -= f is phase += (-f) bit for bit, so the direction is a sign flip of f (off the phase chain), not a
+        // select between two sums on it
+        auto signed_f = [&]() { return __uint_as_float(__float_as_uint(f) ^ flip); };
         auto step = [&]() -> float { // ChirpGenerator.hpp:33-46
             f = __fadd_rn(f, sw.f_step);
             if (f > sw.f_max) f = __fsub_rn(f, span);
-            phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
+            phase = __fadd_rn(phase, signed_f());
             return phase;
         };
         auto finish_segment = [&]() { // :48
@@ -221,7 +232,7 @@ __device__ __forceinline__ void chirp_one_packet(const SegFn& segment, int n_seg
 #pragma unroll
                     for (int i = 0; i < CHIRP_CHUNK; ++i) {
                         f = __fadd_rn(f, sw.f_step);
-                        phase = down ? __fsub_rn(phase, f) : __fadd_rn(phase, f);
+                        phase = __fadd_rn(phase, signed_f());
                         if (i == lane) mine = phase;
                     }
                 } else {
